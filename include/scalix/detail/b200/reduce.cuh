@@ -1,0 +1,286 @@
+// scalix-b200: reductions for sm_100a.
+//
+//  * reduce_kernel            whole-slice fold to one value (one pass, 128-bit loads).
+//                             Replaces thrust::reduce at
+//                             /root/reference scalix/algorithm/reduce.cuh:73-79 and is
+//                             pass A (per-partition total) of the multi-device scan.
+//  * reduce_last_dim_kernel   out[s] = fold_j in[s + stride*j] for ALL rows s in one
+//                             pass that reads every byte once, coalesced.  Replaces the
+//                             `stride` serial strided thrust::reduce calls at
+//                             /root/reference scalix/algorithm/reduce_last_dim.cuh:189-206.
+//  * fold_rows_kernel         deterministic fixed-order fold of per-partition rows
+//                             (replaces the mutex-ordered host fold, ibid. :208-211).
+//
+// All folds run in a fixed order that depends only on (shape, grid), so float
+// results are bit-stable run to run.  Operators must be associative and
+// commutative (as thrust::reduce requires of the reference's callers).
+#pragma once
+
+#include "primitives.cuh"
+
+namespace sclx::b200 {
+
+// block-wide fold; result valid in thread 0.  `smem` holds THREADS/32 values.
+template<class T, class Op, int THREADS>
+__device__ __forceinline__ T block_reduce(T x, Op& op, T* smem) {
+    constexpr int WARPS = THREADS / 32;
+    const int lane      = threadIdx.x & 31;
+    const int warp      = threadIdx.x >> 5;
+    x                   = warp_reduce(x, op);
+    if (lane == 0) smem[warp] = x;
+    __syncthreads();
+    if (warp == 0) {
+        T y = smem[lane < WARPS ? lane : 0];
+#pragma unroll
+        for (int d = 16; d > 0; d >>= 1) {
+            T z = shfl_down(y, d);
+            if (lane + d < WARPS) y = op(y, z);
+        }
+        x = y;
+    }
+    return x;
+}
+
+struct reduce_workspace_t {
+    void* partials;          // gridDim.x values (reduce) or gridDim.x*rows (last_dim)
+    unsigned* ticket;        // zero-initialised, self-resetting
+};
+
+// ---------------------------------------------------------------------------
+// whole-slice reduce
+// ---------------------------------------------------------------------------
+template<class T, class Op, int THREADS, int VECS, bool ALIGNED>
+__global__ void __launch_bounds__(THREADS) reduce_kernel(
+    const T* __restrict__ in,
+    size_t n,
+    T identity,
+    T* __restrict__ out,  // one value; receives op(identity-seeded fold)
+    reduce_workspace_t ws,
+    Op op
+) {
+    constexpr int V = vec_traits<T>::width;
+    __shared__ T s_red[THREADS / 32];
+    __shared__ bool s_last;
+
+    T acc[VECS];
+#pragma unroll
+    for (int k = 0; k < VECS; ++k) acc[k] = identity;
+
+    const size_t nvec        = ALIGNED ? n / V : 0;
+    const size_t step        = size_t(gridDim.x) * THREADS;
+    const size_t first       = size_t(blockIdx.x) * THREADS + threadIdx.x;
+    if constexpr (ALIGNED && V > 1) {
+        size_t i = first;
+        // VECS independent 128-bit loads in flight per thread
+        for (; i + (VECS - 1) * step < nvec; i += VECS * step) {
+            vec_t<T, V> v[VECS];
+#pragma unroll
+            for (int k = 0; k < VECS; ++k)
+                v[k] = load_vec_stream<T, V>(in + (i + k * step) * V);
+#pragma unroll
+            for (int k = 0; k < VECS; ++k) {
+#pragma unroll
+                for (int e = 0; e < V; ++e) acc[k] = op(acc[k], v[k].v[e]);
+            }
+        }
+        for (; i < nvec; i += step) {
+            vec_t<T, V> v = load_vec_stream<T, V>(in + i * V);
+#pragma unroll
+            for (int e = 0; e < V; ++e) acc[0] = op(acc[0], v.v[e]);
+        }
+    }
+    // scalar tail (or the whole range when unaligned)
+    for (size_t i = nvec * V + first; i < n; i += step) acc[0] = op(acc[0], in[i]);
+
+#pragma unroll
+    for (int k = 1; k < VECS; ++k) acc[0] = op(acc[0], acc[k]);
+
+    T block = block_reduce<T, Op, THREADS>(acc[0], op, s_red);
+
+    T* partials = static_cast<T*>(ws.partials);
+    if (threadIdx.x == 0) {
+        partials[blockIdx.x] = block;
+        __threadfence();
+        unsigned t = atomicAdd(ws.ticket, 1u);
+        s_last     = (t == gridDim.x - 1);
+    }
+    __syncthreads();
+    if (!s_last) return;
+    __threadfence();
+    // last CTA: fixed-order fold of the per-CTA partials
+    T a = identity;
+    for (unsigned i = threadIdx.x; i < gridDim.x; i += THREADS)
+        a = op(a, load_cg(partials + i));
+    __syncthreads();
+    a = block_reduce<T, Op, THREADS>(a, op, s_red);
+    if (threadIdx.x == 0) {
+        *out       = a;
+        *ws.ticket = 0;  // ready for the next launch on this stream
+    }
+}
+
+// ---------------------------------------------------------------------------
+// reduce along the last (slowest, partitioned) dimension
+// ---------------------------------------------------------------------------
+// Memory is [cols][rows] with rows contiguous (rows = product of the leading
+// dims = the reference's `stride`).  Work unit = one vector of VW elements
+// (VW = 16/sizeof(T) when rows % VW == 0 and the base is 16-byte aligned, else 1).
+// slots = rows / VW vectors per column.
+//   slots <= THREADS : `active` = floor(THREADS/slots)*slots threads, thread t keeps
+//                      slot t % slots for its whole life and walks columns, so its
+//                      VW accumulators live in registers; consecutive threads read
+//                      consecutive vectors (fully coalesced).
+//   slots  > THREADS : blockIdx.y selects a band of THREADS slots.
+template<class T, class Op, int THREADS, int UNROLL, int VW>
+__global__ void __launch_bounds__(THREADS) reduce_last_dim_kernel(
+    const T* __restrict__ in,
+    size_t rows,
+    size_t cols,
+    T identity,
+    T* __restrict__ out,  // rows values
+    reduce_workspace_t ws,
+    Op op
+) {
+    extern __shared__ __align__(16) unsigned char s_raw[];
+    T* s_acc = reinterpret_cast<T*>(s_raw);  // [groups][slots_in_band*VW]
+    __shared__ bool s_last;
+
+    const size_t slots = rows / VW;
+    const int tid      = threadIdx.x;
+
+    size_t band_first, band_slots;  // slots handled by this CTA
+    int groups;                     // column groups processed side by side
+    if (slots <= THREADS) {
+        band_first = 0;
+        band_slots = slots;
+        groups     = int(THREADS / slots);
+    } else {
+        band_first = size_t(blockIdx.y) * THREADS;
+        band_slots = (slots - band_first < THREADS) ? slots - band_first : THREADS;
+        groups     = 1;
+    }
+    const int active = int(groups * band_slots);
+    const int slot   = int(tid % band_slots);
+    const int group  = int(tid / band_slots);
+
+    T acc[UNROLL][VW];
+#pragma unroll
+    for (int u = 0; u < UNROLL; ++u)
+#pragma unroll
+        for (int e = 0; e < VW; ++e) acc[u][e] = identity;
+
+    if (tid < active) {
+        const size_t col_step = size_t(gridDim.x) * groups;
+        size_t c              = size_t(blockIdx.x) * groups + group;
+        const T* base         = in + (band_first + slot) * VW;
+        for (; c + (UNROLL - 1) * col_step < cols; c += UNROLL * col_step) {
+            if constexpr (VW > 1) {
+                vec_t<T, VW> v[UNROLL];
+#pragma unroll
+                for (int u = 0; u < UNROLL; ++u)
+                    v[u] = load_vec_stream<T, VW>(base + (c + u * col_step) * rows);
+#pragma unroll
+                for (int u = 0; u < UNROLL; ++u)
+#pragma unroll
+                    for (int e = 0; e < VW; ++e) acc[u][e] = op(acc[u][e], v[u].v[e]);
+            } else {
+                T v[UNROLL];
+#pragma unroll
+                for (int u = 0; u < UNROLL; ++u)
+                    v[u] = __ldg(base + (c + u * col_step) * rows);
+#pragma unroll
+                for (int u = 0; u < UNROLL; ++u) acc[u][0] = op(acc[u][0], v[u]);
+            }
+        }
+        for (; c < cols; c += col_step) {
+#pragma unroll
+            for (int e = 0; e < VW; ++e) acc[0][e] = op(acc[0][e], base[c * rows + e]);
+        }
+        // pairwise fold of the unrolled accumulators
+#pragma unroll
+        for (int w = 1; w < UNROLL; w <<= 1)
+#pragma unroll
+            for (int u = 0; u + w < UNROLL; u += 2 * w)
+#pragma unroll
+                for (int e = 0; e < VW; ++e) acc[u][e] = op(acc[u][e], acc[u + w][e]);
+#pragma unroll
+        for (int e = 0; e < VW; ++e)
+            s_acc[(size_t(group) * band_slots + slot) * VW + e] = acc[0][e];
+    }
+    __syncthreads();
+
+    // fold the column groups (tree over groups, fixed order), then publish
+    const size_t band_elems = band_slots * VW;
+    T* partials             = static_cast<T*>(ws.partials);
+    for (size_t r = tid; r < band_elems; r += THREADS) {
+        T a = s_acc[r];
+        for (int g = 1; g < groups; ++g) a = op(a, s_acc[size_t(g) * band_elems + r]);
+        partials[size_t(blockIdx.x) * rows + band_first * VW + r] = a;
+    }
+    __threadfence();
+    __syncthreads();
+    if (tid == 0) {
+        unsigned t = atomicAdd(ws.ticket, 1u);
+        s_last     = (t == gridDim.x * gridDim.y - 1);
+    }
+    __syncthreads();
+    if (!s_last) return;
+    __threadfence();
+
+    // last CTA: out[r] = identity (+) partial[0][r] (+) partial[1][r] ...
+    // pairwise over 4 interleaved chains to shorten the float dependency chain
+    for (size_t r = tid; r < rows; r += THREADS) {
+        T a0 = identity, a1 = identity, a2 = identity, a3 = identity;
+        unsigned b = 0;
+        for (; b + 3 < gridDim.x; b += 4) {
+            a0 = op(a0, load_cg(partials + size_t(b) * rows + r));
+            a1 = op(a1, load_cg(partials + size_t(b + 1) * rows + r));
+            a2 = op(a2, load_cg(partials + size_t(b + 2) * rows + r));
+            a3 = op(a3, load_cg(partials + size_t(b + 3) * rows + r));
+        }
+        for (; b < gridDim.x; ++b)
+            a0 = op(a0, load_cg(partials + size_t(b) * rows + r));
+        out[r] = op(op(a0, a1), op(a2, a3));
+    }
+    if (tid == 0) *ws.ticket = 0;
+}
+
+// out[r] = fold over p (fixed order 0..nparts-1) of parts[p][r], seeded with identity
+// (/root/reference scalix/algorithm/reduce_last_dim.cuh:177,208-211: result is filled
+// with identity, then every device's partial row is folded in).
+template<class T, class Op>
+__global__ void fold_rows_kernel(
+    const T* const* __restrict__ parts,  // nparts row pointers (may be peer memory)
+    int nparts,
+    size_t rows,
+    T identity,
+    T* __restrict__ out,
+    Op op
+) {
+    for (size_t r = size_t(blockIdx.x) * blockDim.x + threadIdx.x; r < rows;
+         r += size_t(gridDim.x) * blockDim.x) {
+        T a = identity;
+        for (int p = 0; p < nparts; ++p) a = op(a, parts[p][r]);
+        out[r] = a;
+    }
+}
+
+// contiguous variant: parts laid out [nparts][rows] (e.g. an NCCL all-gather buffer)
+template<class T, class Op>
+__global__ void fold_rows_contig_kernel(
+    const T* __restrict__ parts,
+    int nparts,
+    size_t rows,
+    T identity,
+    T* __restrict__ out,
+    Op op
+) {
+    for (size_t r = size_t(blockIdx.x) * blockDim.x + threadIdx.x; r < rows;
+         r += size_t(gridDim.x) * blockDim.x) {
+        T a = identity;
+        for (int p = 0; p < nparts; ++p) a = op(a, parts[size_t(p) * rows + r]);
+        out[r] = a;
+    }
+}
+
+}  // namespace sclx::b200

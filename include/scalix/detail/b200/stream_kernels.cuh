@@ -1,0 +1,147 @@
+// scalix-b200: framework-owned streaming kernels whose access pattern is known,
+// so they use 128-bit accesses directly instead of going through the per-element
+// lambda dispatcher.
+//
+//  * fill_kernel   arr[i] = value          (/root/reference scalix/fill.cuh:40-51)
+//  * iota_kernel   arr[i] = T(start) + i   (/root/reference scalix/iota.cuh:40-51)
+//  * gather_kernel out[i] = src[idx[i]]    (the access pattern of
+//                  /root/reference examples/scaling_performance.cu:59-78 and
+//                  examples/distributed_indexing.cu:146-154 with the arithmetic removed)
+#pragma once
+
+#include "primitives.cuh"
+
+namespace sclx::b200 {
+
+// Fill [out, out+n) with `value`.  Handles any alignment: scalar head up to the
+// first 16-byte boundary, 128-bit body, scalar tail.
+template<class T, int THREADS, int UNROLL>
+__global__ void __launch_bounds__(THREADS)
+    fill_kernel(T* __restrict__ out, size_t n, T value) {
+    constexpr int V = vec_traits<T>::width;
+    const size_t gtid = size_t(blockIdx.x) * THREADS + threadIdx.x;
+    const size_t gstride = size_t(gridDim.x) * THREADS;
+
+    size_t head = 0;
+    if constexpr (V > 1) {
+        const uintptr_t a = reinterpret_cast<uintptr_t>(out);
+        head              = ((16 - (a & 15u)) & 15u) / sizeof(T);
+        if (head > n) head = n;
+        const size_t nvec = (n - head) / V;
+        vec_t<T, V> v;
+#pragma unroll
+        for (int e = 0; e < V; ++e) v.v[e] = value;
+        T* body  = out + head;
+        size_t i = gtid;
+        for (; i + (UNROLL - 1) * gstride < nvec; i += UNROLL * gstride) {
+#pragma unroll
+            for (int u = 0; u < UNROLL; ++u)
+                store_vec<T, V>(body + (i + u * gstride) * V, v);
+        }
+        for (; i < nvec; i += gstride) store_vec<T, V>(body + i * V, v);
+        // scalar head and tail
+        if (gtid < head) out[gtid] = value;
+        const size_t tail0 = head + nvec * V;
+        if (tail0 + gtid < n) out[tail0 + gtid] = value;
+    } else {
+        for (size_t i = gtid; i < n; i += gstride) out[i] = value;
+    }
+}
+
+// arr[i] = start + T(first_index + i): `first_index` is the partition's offset in
+// the whole array so every device writes its own slice of one global sequence.
+template<class T, int THREADS, int UNROLL>
+__global__ void __launch_bounds__(THREADS)
+    iota_kernel(T* __restrict__ out, size_t n, T start, size_t first_index) {
+    constexpr int V = vec_traits<T>::width;
+    const size_t gtid = size_t(blockIdx.x) * THREADS + threadIdx.x;
+    const size_t gstride = size_t(gridDim.x) * THREADS;
+
+    if constexpr (V > 1) {
+        const uintptr_t a = reinterpret_cast<uintptr_t>(out);
+        size_t head       = ((16 - (a & 15u)) & 15u) / sizeof(T);
+        if (head > n) head = n;
+        const size_t nvec = (n - head) / V;
+        T* body           = out + head;
+        size_t i          = gtid;
+        for (; i + (UNROLL - 1) * gstride < nvec; i += UNROLL * gstride) {
+#pragma unroll
+            for (int u = 0; u < UNROLL; ++u) {
+                const size_t e0 = first_index + head + (i + u * gstride) * V;
+                vec_t<T, V> v;
+#pragma unroll
+                for (int e = 0; e < V; ++e) v.v[e] = start + static_cast<T>(e0 + e);
+                store_vec<T, V>(body + (i + u * gstride) * V, v);
+            }
+        }
+        for (; i < nvec; i += gstride) {
+            const size_t e0 = first_index + head + i * V;
+            vec_t<T, V> v;
+#pragma unroll
+            for (int e = 0; e < V; ++e) v.v[e] = start + static_cast<T>(e0 + e);
+            store_vec<T, V>(body + i * V, v);
+        }
+        if (gtid < head) out[gtid] = start + static_cast<T>(first_index + gtid);
+        const size_t tail0 = head + nvec * V;
+        if (tail0 + gtid < n)
+            out[tail0 + gtid] = start + static_cast<T>(first_index + tail0 + gtid);
+    } else {
+        for (size_t i = gtid; i < n; i += gstride)
+            out[i] = start + static_cast<T>(first_index + i);
+    }
+}
+
+// Partition table for gathers whose source is split over several devices and
+// NOT mapped into one contiguous virtual range (multi-process ranks that opened
+// each other's slices through CUDA IPC).  Element e lives in
+// part[e / elems_per_part] at offset e % elems_per_part.
+struct gather_parts_t {
+    const void* part[8];
+    unsigned long long elems_per_part;  // ceil(last/ndev) * leading elements
+    int nparts;                         // 1: plain pointer in part[0]
+};
+
+// out[i] = src[idx[i]].  Each thread keeps UNROLL independent random loads in
+// flight; index reads are 128-bit coalesced.
+template<class T, class I, int THREADS, int UNROLL>
+__global__ void __launch_bounds__(THREADS) gather_kernel(
+    const I* __restrict__ idx,
+    size_t n,
+    gather_parts_t src,
+    T* __restrict__ out
+) {
+    const size_t gtid    = size_t(blockIdx.x) * THREADS + threadIdx.x;
+    const size_t gstride = size_t(gridDim.x) * THREADS;
+    size_t i             = gtid;
+    for (; i + (UNROLL - 1) * gstride < n; i += UNROLL * gstride) {
+        I j[UNROLL];
+#pragma unroll
+        for (int u = 0; u < UNROLL; ++u) j[u] = __ldg(idx + i + u * gstride);
+        T v[UNROLL];
+#pragma unroll
+        for (int u = 0; u < UNROLL; ++u) {
+            if (src.nparts == 1) {
+                v[u] = __ldg(static_cast<const T*>(src.part[0]) + j[u]);
+            } else {
+                const unsigned long long e = (unsigned long long)j[u];
+                const unsigned long long p = e / src.elems_per_part;
+                const unsigned long long o = e - p * src.elems_per_part;
+                v[u] = __ldg(static_cast<const T*>(src.part[p]) + o);
+            }
+        }
+#pragma unroll
+        for (int u = 0; u < UNROLL; ++u) out[i + u * gstride] = v[u];
+    }
+    for (; i < n; i += gstride) {
+        const unsigned long long e = (unsigned long long)__ldg(idx + i);
+        if (src.nparts == 1) {
+            out[i] = __ldg(static_cast<const T*>(src.part[0]) + e);
+        } else {
+            const unsigned long long p = e / src.elems_per_part;
+            const unsigned long long o = e - p * src.elems_per_part;
+            out[i] = __ldg(static_cast<const T*>(src.part[p]) + o);
+        }
+    }
+}
+
+}  // namespace sclx::b200
