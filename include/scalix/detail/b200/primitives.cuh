@@ -33,7 +33,7 @@ struct alignas(sizeof(T) * V >= 16 ? 16 : sizeof(T) * V) vec_t {
 };
 
 template<class T>
-__device__ __forceinline__ bool is_aligned16(const T* p) {
+__host__ __device__ __forceinline__ bool is_aligned16(const T* p) {
     return (reinterpret_cast<uintptr_t>(p) & 15u) == 0;
 }
 

@@ -45,7 +45,20 @@ def build(force=False, verbose=False):
     if procs or not os.path.exists(LIB):
         cmd = ["nvcc", "-shared", "-gencode", "arch=compute_100a,code=sm_100a", "-o", LIB, *objs]
         subprocess.check_call(cmd)
+        _check_no_exit_stubs()
     return LIB
+
+
+def _check_no_exit_stubs():
+    """nvcc turns a host-side call of a __device__-only function into exit(1) at run time
+    instead of a compile error; refuse to ship a library that contains one."""
+    try:
+        dis = subprocess.run(["objdump", "-d", LIB], capture_output=True, text=True).stdout
+    except FileNotFoundError:
+        return
+    if "<exit@plt>" in dis:
+        os.remove(LIB)
+        raise RuntimeError("libscalix_b200.so calls exit(): a __device__ function is used from host code")
 
 
 if __name__ == "__main__":

@@ -355,6 +355,46 @@ int launch_gather(const I* idx, size_t n, const gather_parts_t& parts, T* out,
     return 0;
 }
 
+// NOTE: these are named functors, not generic lambdas, on purpose: nvcc replaces a kernel
+// launch whose instantiation it first meets inside a generic lambda body by exit(1).
+struct scan_call {
+    const void* in; void* out; size_t n; const void* lower; int n_lower; void* total_out;
+    cudaStream_t stream;
+    template<class T, class Op>
+    int operator()(T, Op o) const {
+        return launch_scan<T, Op>((const T*)in, (T*)out, n, (const T*)lower, n_lower, (T*)total_out,
+                                  stream, o);
+    }
+};
+struct reduce_call {
+    const void* in; size_t n; const void* identity; void* out; cudaStream_t stream;
+    template<class T, class Op>
+    int operator()(T, Op o) const {
+        return launch_reduce<T, Op>((const T*)in, n, load_scalar<T>(identity), (T*)out, stream, o);
+    }
+};
+struct rld_call {
+    const void* in; size_t rows, cols; const void* identity; void* out; cudaStream_t stream;
+    template<class T, class Op>
+    int operator()(T, Op o) const {
+        return launch_reduce_last_dim<T, Op>((const T*)in, rows, cols, load_scalar<T>(identity),
+                                             (T*)out, stream, o);
+    }
+};
+struct fold_call {
+    const void* parts; int nparts; size_t rows; const void* identity; void* out;
+    cudaStream_t stream;
+    template<class T, class Op>
+    int operator()(T, Op o) const {
+        unsigned grid = unsigned((rows + 255) / 256);
+        if (grid > 1184) grid = 1184;
+        fold_rows_contig_kernel<T, Op><<<grid, 256, 0, stream>>>(
+            (const T*)parts, nparts, rows, load_scalar<T>(identity), (T*)out, o);
+        SCLX_LAUNCHED();
+        return 0;
+    }
+};
+
 struct alignas(16) bytes16 {
     unsigned long long a, b;
 };
@@ -514,33 +554,21 @@ int sclx_b200_inclusive_scan(const void* in, void* out, size_t n, int dtype, int
         return fail(SCLX_E_INVALID_ARGUMENT, "inclusive_scan: null pointer");
     if (n_lower < 0 || (n_lower > 0 && !lower_totals))
         return fail(SCLX_E_INVALID_ARGUMENT, "inclusive_scan: bad carry arguments");
-    return dispatch(dtype, op, [&](auto t, auto o) {
-        using T = decltype(t);
-        return launch_scan<T>((const T*)in, (T*)out, n, (const T*)lower_totals, n_lower,
-                              (T*)total_out, (cudaStream_t)stream, o);
-    });
+    return dispatch(dtype, op, scan_call{in, out, n, lower_totals, n_lower, total_out, (cudaStream_t)stream});
 }
 
 int sclx_b200_reduce(const void* in, size_t n, int dtype, int op, const void* identity,
                      void* out, void* stream) {
     if (!identity || !out || (!in && n))
         return fail(SCLX_E_INVALID_ARGUMENT, "reduce: null pointer");
-    return dispatch(dtype, op, [&](auto t, auto o) {
-        using T = decltype(t);
-        return launch_reduce<T>((const T*)in, n, load_scalar<T>(identity), (T*)out,
-                                (cudaStream_t)stream, o);
-    });
+    return dispatch(dtype, op, reduce_call{in, n, identity, out, (cudaStream_t)stream});
 }
 
 int sclx_b200_reduce_last_dim(const void* in, size_t rows, size_t cols, int dtype, int op,
                               const void* identity, void* out, void* stream) {
     if (!identity || (!out && rows) || (!in && rows * cols))
         return fail(SCLX_E_INVALID_ARGUMENT, "reduce_last_dim: null pointer");
-    return dispatch(dtype, op, [&](auto t, auto o) {
-        using T = decltype(t);
-        return launch_reduce_last_dim<T>((const T*)in, rows, cols, load_scalar<T>(identity),
-                                         (T*)out, (cudaStream_t)stream, o);
-    });
+    return dispatch(dtype, op, rld_call{in, rows, cols, identity, out, (cudaStream_t)stream});
 }
 
 int sclx_b200_fold_rows(const void* parts, int nparts, size_t rows, int dtype, int op,
@@ -548,15 +576,7 @@ int sclx_b200_fold_rows(const void* parts, int nparts, size_t rows, int dtype, i
     if (nparts < 0 || !identity || (!out && rows) || (!parts && nparts && rows))
         return fail(SCLX_E_INVALID_ARGUMENT, "fold_rows: bad arguments");
     if (rows == 0) return 0;
-    return dispatch(dtype, op, [&](auto t, auto o) {
-        using T = decltype(t);
-        unsigned grid = unsigned((rows + 255) / 256);
-        if (grid > 1184) grid = 1184;
-        fold_rows_contig_kernel<T><<<grid, 256, 0, (cudaStream_t)stream>>>(
-            (const T*)parts, nparts, rows, load_scalar<T>(identity), (T*)out, o);
-        SCLX_LAUNCHED();
-        return 0;
-    });
+    return dispatch(dtype, op, fold_call{parts, nparts, rows, identity, out, (cudaStream_t)stream});
 }
 
 int sclx_b200_gather(const void* idx, size_t n, int idx_bytes, const void* const* src_parts,
