@@ -89,7 +89,7 @@ def test_scan_multiplies_wraps(sclx, oracle):
     a = (np.arange(5000, dtype=np.uint32) * 2 + 3).astype(np.uint32)
     d_in, d_out = dev(sclx, a), sclx.DeviceBuffer(a.nbytes)
     sclx.inclusive_scan(d_in, d_out, a.size, sclx.U32, sclx.MULTIPLIES)
-    assert np.array_equal(d_out.to_numpy(np.uint32), oracle.inclusive_scan(a, oracle.U32, oracle.MUL))
+    assert np.array_equal(d_out.to_numpy(np.uint32), oracle.inclusive_scan(a, oracle.U32, oracle.MULTIPLIES))
 
 
 @pytest.mark.parametrize("n", [0])
