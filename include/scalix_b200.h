@@ -167,6 +167,49 @@ int sclx_b200_reduce_last_dim_host(const void* host_in, size_t rows, size_t cols
 int sclx_b200_inclusive_scan_host(const void* host_in, void* host_out, size_t n, int dtype,
                                   int op);
 
+/* ---- runtime under the sclx:: header API (include/scalix/) --------------------------------------
+ * Logical devices are the physical GPUs, or N emulated devices on GPU 0 when
+ * SCLX_B200_EMULATE_DEVICES=N / sclx_b200_rt_set_emulated_devices(N) is set before first use
+ * (the equivalent of SCALIX_EMULATE_MULTIDEVICE, /root/reference CMakeLists.txt:31-44). */
+int sclx_b200_rt_init(void);
+int sclx_b200_rt_set_emulated_devices(int n);
+int sclx_b200_rt_device_count(void);              /* logical devices */
+int sclx_b200_rt_physical_device(int logical);
+void* sclx_b200_rt_stream(int logical);           /* the device's persistent stream (cudaStream_t) */
+int sclx_b200_rt_sm_count(int logical);
+
+/* One array = one contiguous virtual range whose pages are explicit physical allocations on
+ * the partitions' devices, mapped read/write into every device (peer loads/stores over NVLink)
+ * and shadowed by an on-demand host mirror at the same addresses.  Replaces
+ * cudaMallocManaged + cudaMemAdvise + cudaMemPrefetchAsync of
+ * /root/reference scalix/array.cuh:241-248,517-615.  Partition p starts at byte_starts[p]
+ * (byte_starts[0] == 0) and lives on logical device devices[p].  Memory is zero-filled. */
+int sclx_b200_array_create(size_t bytes, int nparts, const int* devices, const size_t* byte_starts,
+                           void** base);
+int sclx_b200_array_free(void* base);
+/* array::set_primary_devices on a live array: moves the pages, keeps pointer and contents */
+int sclx_b200_array_repartition(void* base, int nparts, const int* devices,
+                                const size_t* byte_starts);
+int sclx_b200_array_owner(const void* ptr);       /* logical device holding the page, or -1 */
+
+/* host/device coherence of the mirror */
+int sclx_b200_rt_before_device_access(void);      /* write back host stores, drop host copies */
+int sclx_b200_rt_prefetch_to_host(const void* ptr, size_t bytes);
+int sclx_b200_rt_quiesce(void);                   /* wait for all device work */
+unsigned long long sclx_b200_rt_host_faults(void);
+
+/* launch groups: replaces the stream-per-launch + synchronise-all of
+ * /root/reference scalix/detail/execute_kernel.cuh:110-115,197-199 */
+int sclx_b200_rt_begin_launch(int ndev, const int* devices);
+int sclx_b200_rt_end_launch(int ndev, const int* devices);
+int sclx_b200_rt_stream_wait(int waiter, int signaller);
+int sclx_b200_rt_sync_devices(int ndev, const int* devices);
+
+/* per-device workspaces of the scan / reduce kernels (valid in stream order on that device) */
+int sclx_b200_rt_scan_workspace(int logical, size_t tiles, void** desc, unsigned* epoch);
+int sclx_b200_rt_reduce_workspace(int logical, size_t bytes, void** partials, void** ticket);
+int sclx_b200_rt_scratch(size_t bytes, void** ptr); /* small peer-visible scratch */
+
 /* number of kernels this library has launched in this process (monotonic) */
 unsigned long long sclx_b200_launch_count(void);
 

@@ -62,6 +62,28 @@ ABI = {
     "sclx_b200_reduce_last_dim_host": (_i, [_vp, _sz, _sz, _i, _i, _vp, _vp]),
     "sclx_b200_inclusive_scan_host": (_i, [_vp, _vp, _sz, _i, _i]),
     "sclx_b200_launch_count": (C.c_ulonglong, []),
+    # runtime under the sclx:: header API
+    "sclx_b200_rt_init": (_i, []),
+    "sclx_b200_rt_set_emulated_devices": (_i, [_i]),
+    "sclx_b200_rt_device_count": (_i, []),
+    "sclx_b200_rt_physical_device": (_i, [_i]),
+    "sclx_b200_rt_stream": (_vp, [_i]),
+    "sclx_b200_rt_sm_count": (_i, [_i]),
+    "sclx_b200_array_create": (_i, [_sz, _i, _vp, _vp, _pp]),
+    "sclx_b200_array_free": (_i, [_vp]),
+    "sclx_b200_array_repartition": (_i, [_vp, _i, _vp, _vp]),
+    "sclx_b200_array_owner": (_i, [_vp]),
+    "sclx_b200_rt_before_device_access": (_i, []),
+    "sclx_b200_rt_prefetch_to_host": (_i, [_vp, _sz]),
+    "sclx_b200_rt_quiesce": (_i, []),
+    "sclx_b200_rt_host_faults": (C.c_ulonglong, []),
+    "sclx_b200_rt_begin_launch": (_i, [_i, _vp]),
+    "sclx_b200_rt_end_launch": (_i, [_i, _vp]),
+    "sclx_b200_rt_stream_wait": (_i, [_i, _i]),
+    "sclx_b200_rt_sync_devices": (_i, [_i, _vp]),
+    "sclx_b200_rt_scan_workspace": (_i, [_i, _sz, _pp, _vp]),
+    "sclx_b200_rt_reduce_workspace": (_i, [_i, _sz, _pp, _pp]),
+    "sclx_b200_rt_scratch": (_i, [_sz, _pp]),
 }
 for _name, (_res, _args) in ABI.items():
     _fn = getattr(lib, _name)  # AttributeError here = header and library disagree
