@@ -1,0 +1,133 @@
+// Experiment: geometry sweep of the streaming scan (scan_stream.cuh) against the register
+// look-back kernel (scan.cuh), CUB DeviceScan (both functor flavours) and a D2D copy.
+// Every configuration is checked element-for-element against the CUB result.
+#include "scalix/detail/b200/scan_stream.cuh"
+#include <cub/device/device_scan.cuh>
+#include <thrust/functional.h>
+#include <cuda/std/functional>
+#include <cstdio>
+#include <cstdlib>
+#include <cstring>
+#include <vector>
+using namespace sclx::b200;
+#define CK(x) do { cudaError_t err__ = (x); if (err__ != cudaSuccess) { printf("FAIL %s: %s\n", #x, cudaGetErrorString(err__)); exit(2); } } while (0)
+struct plus_op { template<class T> __host__ __device__ T operator()(const T& a, const T& b) const { return a + b; } };
+
+template<class T>
+__global__ void init_kernel(T* p, size_t n) {
+    for (size_t i = size_t(blockIdx.x) * blockDim.x + threadIdx.x; i < n; i += size_t(gridDim.x) * blockDim.x) {
+        unsigned long long z = i * 0x9E3779B97F4A7C15ull; z ^= z >> 29;
+        p[i] = T(z & 0xFFFF);
+    }
+}
+template<class T>
+__global__ void diff_kernel(const T* a, const T* b, size_t n, unsigned long long* bad) {
+    for (size_t i = size_t(blockIdx.x) * blockDim.x + threadIdx.x; i < n; i += size_t(gridDim.x) * blockDim.x)
+        if (a[i] != b[i]) atomicAdd(bad, 1ull);
+}
+
+static int g_sms = 148;
+
+template<class T, int THREADS, int VECS, int STAGES>
+void run_stream(const T* in, T* out, const T* want, size_t n, void* desc, unsigned& epoch, scan_stream_counters* ctr,
+                unsigned long long* bad, int reps, const char* sel, int force_cps) {
+    char name[64];
+    snprintf(name, sizeof name, "%dx%dx%d", THREADS, VECS, STAGES);
+    if (sel && strcmp(sel, name)) return;
+    using cfg = scan_stream_config<T, THREADS, VECS, STAGES>;
+    auto kern = inclusive_scan_stream_kernel<T, plus_op, THREADS, VECS, STAGES>;
+    if (cfg::smem_bytes > 227 * 1024) return;
+    CK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, int(cfg::smem_bytes)));
+    int occ = 0;
+    CK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, kern, THREADS, cfg::smem_bytes));
+    if (occ < 1) { printf("%-12s does not fit\n", name); return; }
+    int cps = force_cps > 0 && force_cps < occ ? force_cps : occ;
+    size_t tiles = (n + cfg::tile_items - 1) / cfg::tile_items;
+    unsigned grid = unsigned(std::min<size_t>(tiles, size_t(g_sms) * cps));
+    auto launch = [&] {
+        kern<<<grid, THREADS, cfg::smem_bytes>>>(in, out, n, (typename tile_desc<T>::word_t*)desc, ++epoch,
+                                                 scan_carry_t{nullptr, 0}, nullptr, ctr, plus_op{});
+    };
+    CK(cudaMemset(out, 0, n * sizeof(T)));
+    launch();
+    CK(cudaDeviceSynchronize());
+    CK(cudaMemset(bad, 0, 8));
+    diff_kernel<<<1184, 256>>>(out, want, n, bad);
+    unsigned long long hb = 0;
+    CK(cudaMemcpy(&hb, bad, 8, cudaMemcpyDeviceToHost));
+    launch();
+    CK(cudaDeviceSynchronize());
+    cudaEvent_t s, e; cudaEventCreate(&s); cudaEventCreate(&e);
+    cudaEventRecord(s);
+    for (int i = 0; i < reps; ++i) launch();
+    cudaEventRecord(e); CK((cudaEventSynchronize(e)));
+    float ms; cudaEventElapsedTime(&ms, s, e); ms /= reps;
+    cudaFuncAttributes fa; cudaFuncGetAttributes(&fa, kern);
+    printf("stream %-12s T=%zuB  %8.4f ms  %8.1f GB/s  (regs %d, %d CTA/SM of max %d, tile %zu B, smem %zu B) %s\n", name,
+           sizeof(T), ms, 2.0 * n * sizeof(T) / ms / 1e6, fa.numRegs, cps, occ, cfg::tile_bytes, cfg::smem_bytes,
+           hb ? "MISMATCH" : "ok");
+    if (hb) printf("   !!! %llu mismatching elements\n", hb);
+    fflush(stdout);
+}
+
+template<class T, class Op>
+void run_cub(const T* in, T* out, size_t n, int reps, const char* name, Op op) {
+    void* tmp = nullptr; size_t tb = 0;
+    cub::DeviceScan::InclusiveScan(tmp, tb, in, out, op, n);
+    CK(cudaMalloc(&tmp, tb));
+    cudaEvent_t s, e; cudaEventCreate(&s); cudaEventCreate(&e);
+    for (int i = 0; i < 2; ++i) cub::DeviceScan::InclusiveScan(tmp, tb, in, out, op, n);
+    CK(cudaDeviceSynchronize());
+    cudaEventRecord(s);
+    for (int i = 0; i < reps; ++i) cub::DeviceScan::InclusiveScan(tmp, tb, in, out, op, n);
+    cudaEventRecord(e); CK((cudaEventSynchronize(e)));
+    float ms; cudaEventElapsedTime(&ms, s, e); ms /= reps;
+    printf("%-26s T=%zuB  %8.4f ms  %8.1f GB/s\n", name, sizeof(T), ms, 2.0 * n * sizeof(T) / ms / 1e6);
+    cudaFree(tmp);
+}
+
+template<class T>
+void sweep(size_t n, const char* sel, int reps, int cps) {
+    T *in, *out, *want; void* desc; scan_stream_counters* ctr; unsigned long long* bad;
+    CK(cudaMalloc(&in, n * sizeof(T))); CK(cudaMalloc(&out, n * sizeof(T))); CK(cudaMalloc(&want, n * sizeof(T)));
+    CK(cudaMalloc(&desc, (n / 512 + 64) * 16)); CK(cudaMemset(desc, 0, (n / 512 + 64) * 16));
+    CK(cudaMalloc(&ctr, 256)); CK(cudaMemset(ctr, 0, 256));
+    CK(cudaMalloc(&bad, 8));
+    init_kernel<<<1184, 256>>>(in, n);
+    unsigned epoch = 0;
+    {
+        void* tmp = nullptr; size_t tb = 0;
+        cub::DeviceScan::InclusiveScan(tmp, tb, in, want, cuda::std::plus<T>{}, n);
+        CK(cudaMalloc(&tmp, tb));
+        cub::DeviceScan::InclusiveScan(tmp, tb, in, want, cuda::std::plus<T>{}, n);
+        CK(cudaDeviceSynchronize());
+        cudaFree(tmp);
+    }
+#define R(TH, VE, ST) run_stream<T, TH, VE, ST>(in, out, want, n, desc, epoch, ctr, bad, reps, sel, cps)
+    R(256, 5, 3); R(256, 5, 4); R(256, 7, 3); R(256, 9, 3);
+    R(512, 3, 3); R(512, 3, 4); R(512, 5, 2); R(512, 5, 3); R(512, 5, 4); R(512, 5, 5); R(512, 7, 3); R(512, 7, 4); R(512, 9, 3);
+    R(1024, 3, 3); R(1024, 3, 4); R(1024, 5, 2); R(1024, 5, 3);
+    R(768, 5, 3); R(384, 7, 4); R(128, 9, 4); R(128, 7, 4);
+    if (!sel) {
+        run_cub<T>(in, out, n, reps, "cub thrust::plus<>", thrust::plus<void>{});
+        run_cub<T>(in, out, n, reps, "cub cuda::std::plus<T>", cuda::std::plus<T>{});
+        cudaEvent_t s, e; cudaEventCreate(&s); cudaEventCreate(&e);
+        cudaMemcpy(out, in, n * sizeof(T), cudaMemcpyDeviceToDevice);
+        cudaEventRecord(s); for (int i = 0; i < reps; ++i) cudaMemcpyAsync(out, in, n * sizeof(T), cudaMemcpyDeviceToDevice);
+        cudaEventRecord(e); cudaEventSynchronize(e); float ms; cudaEventElapsedTime(&ms, s, e); ms /= reps;
+        printf("%-26s T=%zuB  %8.4f ms  %8.1f GB/s\n", "cudaMemcpy D2D", sizeof(T), ms, 2.0 * n * sizeof(T) / ms / 1e6);
+    }
+    cudaFree(in); cudaFree(out); cudaFree(want); cudaFree(desc); cudaFree(ctr); cudaFree(bad);
+}
+
+int main(int argc, char** argv) {
+    const char* ty  = argc > 1 ? argv[1] : "all";
+    const char* sel = argc > 2 && strcmp(argv[2], "-") ? argv[2] : nullptr;  // e.g. "512x5x3"
+    int reps = argc > 3 ? atoi(argv[3]) : 10;
+    int cps  = argc > 4 ? atoi(argv[4]) : 0;                                  // cap CTAs/SM
+    size_t lg = argc > 5 ? atoi(argv[5]) : 0;
+    cudaDeviceGetAttribute(&g_sms, cudaDevAttrMultiProcessorCount, 0);
+    if (!strcmp(ty, "all") || !strcmp(ty, "i32")) sweep<unsigned>(size_t(1) << (lg ? lg : 29), sel, reps, cps);
+    if (!strcmp(ty, "all") || !strcmp(ty, "i64")) sweep<unsigned long long>(size_t(1) << (lg ? lg : 28), sel, reps, cps);
+    return 0;
+}
