@@ -1,6 +1,9 @@
 // Experiment: geometry sweep of the streaming scan (scan_stream.cuh) against the register
 // look-back kernel (scan.cuh), CUB DeviceScan (both functor flavours) and a D2D copy.
 // Every configuration is checked element-for-element against the CUB result.
+#ifdef STATS
+#define SCLX_SCAN_STATS 1
+#endif
 #include "scalix/detail/b200/scan_stream.cuh"
 #include <cub/device/device_scan.cuh>
 #include <thrust/functional.h>
@@ -28,14 +31,15 @@ __global__ void diff_kernel(const T* a, const T* b, size_t n, unsigned long long
 
 static int g_sms = 148;
 
-template<class T, int THREADS, int VECS, int STAGES>
+template<class T, int VECS, int CHUNKS, int STAGES, int WR, int WS, int LBK, int WLB>
 void run_stream(const T* in, T* out, const T* want, size_t n, void* desc, unsigned& epoch, scan_stream_counters* ctr,
                 unsigned long long* bad, int reps, const char* sel, int force_cps) {
     char name[64];
-    snprintf(name, sizeof name, "%dx%dx%d", THREADS, VECS, STAGES);
+    snprintf(name, sizeof name, "v%dc%ds%d/r%dw%dk%dl%d", VECS, CHUNKS, STAGES, WR, WS, LBK, WLB);
     if (sel && strcmp(sel, name)) return;
-    using cfg = scan_stream_config<T, THREADS, VECS, STAGES>;
-    auto kern = inclusive_scan_stream_kernel<T, plus_op, THREADS, VECS, STAGES>;
+    using cfg = scan_stream_config<T, VECS, CHUNKS, STAGES, WR, WS, WLB>;
+    constexpr int THREADS = cfg::threads;
+    auto kern = inclusive_scan_stream_kernel<T, plus_op, VECS, CHUNKS, STAGES, WR, WS, LBK, WLB>;
     if (cfg::smem_bytes > 227 * 1024) return;
     CK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, int(cfg::smem_bytes)));
     int occ = 0;
@@ -63,6 +67,20 @@ void run_stream(const T* in, T* out, const T* want, size_t n, void* desc, unsign
     cudaEventRecord(e); CK((cudaEventSynchronize(e)));
     float ms; cudaEventElapsedTime(&ms, s, e); ms /= reps;
     cudaFuncAttributes fa; cudaFuncGetAttributes(&fa, kern);
+#ifdef STATS
+    {
+        unsigned long long z[16] = {0}, h[16];
+        cudaMemcpyToSymbol(g_scan_stats, z, sizeof z);
+        launch();
+        CK(cudaDeviceSynchronize());
+        cudaMemcpyFromSymbol(h, g_scan_stats, sizeof h);
+        double t = double(h[7] ? h[7] : 1), per_cta = double(tiles) / grid;
+        printf("    per tile: lookback %.0f cyc, %.2f rounds, %.1f re-polls | per CTA-tile waits: scanner %.0f reducer %.0f loader %.0f storer %.0f cyc\n",
+               h[0] / t, h[1] / t, h[2] / t, h[3] / (per_cta * grid), h[4] / (per_cta * grid), h[5] / (per_cta * grid), h[6] / (per_cta * grid));
+        printf("    stage timeline since load issue (cyc): full %.0f  aggregate %.0f  lb-start %.0f  prefixed %.0f  written %.0f  empty %.0f | period %.0f\n",
+               h[8] / t, h[9] / t, h[10] / t, h[11] / t, h[12] / t, h[13] / t, ms * 1e-3 * 1.92e9 / per_cta);
+    }
+#endif
     printf("stream %-12s T=%zuB  %8.4f ms  %8.1f GB/s  (regs %d, %d CTA/SM of max %d, tile %zu B, smem %zu B) %s\n", name,
            sizeof(T), ms, 2.0 * n * sizeof(T) / ms / 1e6, fa.numRegs, cps, occ, cfg::tile_bytes, cfg::smem_bytes,
            hb ? "MISMATCH" : "ok");
@@ -103,11 +121,10 @@ void sweep(size_t n, const char* sel, int reps, int cps) {
         CK(cudaDeviceSynchronize());
         cudaFree(tmp);
     }
-#define R(TH, VE, ST) run_stream<T, TH, VE, ST>(in, out, want, n, desc, epoch, ctr, bad, reps, sel, cps)
-    R(256, 5, 3); R(256, 5, 4); R(256, 7, 3); R(256, 9, 3);
-    R(512, 3, 3); R(512, 3, 4); R(512, 5, 2); R(512, 5, 3); R(512, 5, 4); R(512, 5, 5); R(512, 7, 3); R(512, 7, 4); R(512, 9, 3);
-    R(1024, 3, 3); R(1024, 3, 4); R(1024, 5, 2); R(1024, 5, 3);
-    R(768, 5, 3); R(384, 7, 4); R(128, 9, 4); R(128, 7, 4);
+#define R(VE, CH, ST, WR, WS, K, L) run_stream<T, VE, CH, ST, WR, WS, K, L>(in, out, want, n, desc, epoch, ctr, bad, reps, sel, cps)
+    R(5, 16, 5, 8, 16, 1, 1); R(5, 16, 5, 8, 16, 2, 1); R(5, 16, 5, 8, 16, 3, 1); R(5, 16, 5, 8, 20, 2, 1); R(5, 16, 5, 6, 12, 2, 1); R(5, 16, 5, 12, 16, 2, 1);
+    R(9, 8, 6, 8, 16, 2, 1); R(5, 8, 10, 8, 16, 2, 1); R(5, 12, 7, 8, 12, 2, 1); R(3, 32, 4, 8, 16, 2, 1); R(7, 16, 3, 8, 16, 2, 1); R(7, 12, 5, 8, 16, 2, 1);
+    R(5, 20, 4, 8, 16, 2, 1); R(5, 18, 4, 8, 16, 2, 1); R(5, 14, 6, 8, 16, 2, 1); R(3, 24, 6, 8, 16, 2, 1); R(5, 22, 4, 8, 16, 2, 1);
     if (!sel) {
         run_cub<T>(in, out, n, reps, "cub thrust::plus<>", thrust::plus<void>{});
         run_cub<T>(in, out, n, reps, "cub cuda::std::plus<T>", cuda::std::plus<T>{});

@@ -53,10 +53,14 @@ struct tile_desc<T, true> {
     static __device__ __forceinline__ void
     load(const word_t* p, unsigned& status, T& value) {
         word_t w;
+#ifdef SCLX_SCAN_WEAK_POLL
+        asm volatile("ld.global.cg.u64 %0, [%1];" : "=l"(w) : "l"(p) : "memory");
+#else
         asm volatile("ld.relaxed.gpu.global.u64 %0, [%1];"
                      : "=l"(w)
                      : "l"(p)
                      : "memory");
+#endif
         status        = unsigned(w >> 32);
         unsigned bits = unsigned(w);
         memcpy(&value, &bits, sizeof(T));
@@ -83,10 +87,14 @@ struct tile_desc<T, false> {
     static __device__ __forceinline__ void
     load(const word_t* p, unsigned& status, T& value) {
         unsigned long long s, bits;
+#ifdef SCLX_SCAN_WEAK_POLL
+        asm volatile("ld.global.cg.v2.u64 {%0, %1}, [%2];" : "=l"(s), "=l"(bits) : "l"(p) : "memory");
+#else
         asm volatile("ld.relaxed.gpu.global.v2.u64 {%0, %1}, [%2];"
                      : "=l"(s), "=l"(bits)
                      : "l"(p)
                      : "memory");
+#endif
         status = unsigned(s);
         memcpy(&value, &bits, 8);
     }

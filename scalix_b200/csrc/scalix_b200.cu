@@ -5,7 +5,7 @@
 #include "scalix_b200.h"
 
 #include "scalix/detail/b200/reduce.cuh"
-#include "scalix/detail/b200/scan.cuh"
+#include "scalix/detail/b200/scan_stream.cuh"
 #include "scalix/detail/b200/stream_kernels.cuh"
 
 #include <atomic>
@@ -84,6 +84,7 @@ struct device_state {
     void* partials      = nullptr;
     size_t part_bytes   = 0;
     unsigned* ticket    = nullptr;
+    scan_stream_counters* scan_counters = nullptr;  // tile tickets of the streaming scan
     void* ptr_table     = nullptr;  // small device scratch
     cudaStream_t last_stream = nullptr;
     bool has_last            = false;
@@ -105,6 +106,7 @@ int current_state(device_state** out) {
         SCLX_CUDA(cudaEventCreateWithFlags(&st.last_done, cudaEventDisableTiming));
         SCLX_CUDA(cudaMalloc(&st.ticket, 256));
         SCLX_CUDA(cudaMemset(st.ticket, 0, 256));
+        st.scan_counters = reinterpret_cast<scan_stream_counters*>(st.ticket + 32);
         st.sm_count = sms;
     }
     *out = &st;
@@ -201,24 +203,39 @@ T load_scalar(const void* p) {
 }
 
 // ---- launch helpers -----------------------------------------------------------------
-constexpr int kScanThreads = 256;
+// Scan geometry (profiles/r01_scan_stream_sweep.txt): the streaming kernel for 16-byte
+// aligned slices, the register look-back kernel for unaligned ones.
+constexpr int kScanThreads = 256;  // register kernel
+constexpr int kScanVecs    = 6;
+
 template<class T>
-constexpr int scan_vecs() {
-    return sizeof(T) == 8 ? 6 : 6;
-}
+struct stream_geometry {  // 4-byte (and narrower) elements
+    static constexpr int vecs = 5, chunks = 16, stages = 5, w_red = 8, w_scan = 16, lb_k = 1;
+};
+template<>
+struct stream_geometry<u64_t> {
+    static constexpr int vecs = 9, chunks = 8, stages = 6, w_red = 8, w_scan = 16, lb_k = 2;
+};
+template<>
+struct stream_geometry<i64_t> : stream_geometry<u64_t> {};
+template<>
+struct stream_geometry<double> : stream_geometry<u64_t> {};
 
 template<class T, class Op>
 int launch_scan(const T* in, T* out, size_t n, const T* lower, int n_lower, T* total_out,
                 cudaStream_t stream, Op op) {
-    constexpr int VECS = scan_vecs<T>();
-    using cfg          = scan_config<T, kScanThreads, VECS>;
-    using desc_io      = tile_desc<T>;
+    using desc_io = tile_desc<T>;
+    using geo     = stream_geometry<T>;
+    using scfg    = scan_stream_config<T, geo::vecs, geo::chunks, geo::stages, geo::w_red, geo::w_scan>;
+    using rcfg    = scan_config<T, kScanThreads, kScanVecs>;
     if (n == 0) return 0;
     device_state* st = nullptr;
     if (int rc = current_state(&st)) return rc;
     std::lock_guard<std::mutex> lock(st->mu);
 
-    const size_t tiles = (n + cfg::tile_items - 1) / cfg::tile_items;
+    const bool aligned     = is_aligned16(in) && is_aligned16(out);
+    const size_t tile_items = aligned ? scfg::tile_items : rcfg::tile_items;
+    const size_t tiles      = (n + tile_items - 1) / tile_items;
     if (tiles > 0x7fffffffull) return fail(SCLX_E_INVALID_ARGUMENT, "scan: partition too large");
     if (int rc = order_after_previous(*st, stream)) return rc;
     const size_t had = st->scan_bytes;
@@ -230,16 +247,27 @@ int launch_scan(const T* in, T* out, size_t n, const T* lower, int n_lower, T* t
         st->scan_epoch = 1;
     }
     scan_carry_t carry{lower, n_lower};
-    auto* desc         = static_cast<typename desc_io::word_t*>(st->scan_desc);
-    const bool aligned = is_aligned16(in) && is_aligned16(out);
-    if (aligned)
-        inclusive_scan_kernel<T, Op, kScanThreads, VECS, true>
+    auto* desc = static_cast<typename desc_io::word_t*>(st->scan_desc);
+    if (aligned) {
+        auto kernel = inclusive_scan_stream_kernel<T, Op, geo::vecs, geo::chunks, geo::stages,
+                                                   geo::w_red, geo::w_scan, geo::lb_k>;
+        static bool configured[kMaxDevices] = {};
+        int dev = 0;
+        SCLX_CUDA(cudaGetDevice(&dev));
+        if (!configured[dev]) {
+            SCLX_CUDA(cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                           int(scfg::smem_bytes)));
+            configured[dev] = true;
+        }
+        // one persistent CTA per SM (the ring takes the whole shared memory)
+        const unsigned grid = unsigned(tiles < size_t(st->sm_count) ? tiles : size_t(st->sm_count));
+        kernel<<<grid, scfg::threads, scfg::smem_bytes, stream>>>(
+            in, out, n, desc, st->scan_epoch, carry, total_out, st->scan_counters, op);
+    } else {
+        inclusive_scan_kernel<T, Op, kScanThreads, kScanVecs, false>
             <<<unsigned(tiles), kScanThreads, 0, stream>>>(
                 in, out, n, desc, st->scan_epoch, carry, total_out, op);
-    else
-        inclusive_scan_kernel<T, Op, kScanThreads, VECS, false>
-            <<<unsigned(tiles), kScanThreads, 0, stream>>>(
-                in, out, n, desc, st->scan_epoch, carry, total_out, op);
+    }
     SCLX_LAUNCHED();
     return mark_use(*st, stream);
 }
