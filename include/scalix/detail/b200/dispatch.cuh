@@ -43,9 +43,10 @@ __device__ __forceinline__ void advance_index(
     }
 }
 
+// body of the range kernel: shared by sclx_kernel and every REGISTER_SCALIX_KERNEL_TAG kernel
 template<class F, uint RangeRank, uint ThreadBlockRank>
-__global__ void
-sclx_kernel(F f, sclx::kernel_info<RangeRank, ThreadBlockRank> metadata) {
+__device__ __forceinline__ void
+range_kernel_body(F& f, sclx::kernel_info<RangeRank, ThreadBlockRank>& metadata) {
     const sclx::md_range_t<RangeRank>& global_range = metadata.global_range();
     const size_t end    = metadata.start_linear() + metadata.device_range().elements();
     const size_t stride = size_t(gridDim.x) * blockDim.x;
@@ -65,11 +66,13 @@ sclx_kernel(F f, sclx::kernel_info<RangeRank, ThreadBlockRank> metadata) {
     }
 }
 
+// body of the index-generator kernel: every partition walks the whole generator range
+// and acts only on the indices it owns
 template<class F, class IndexGenerator, uint ThreadBlockRank>
-__global__ void sclx_kernel(
-    F f,
-    sclx::kernel_info<IndexGenerator::range_rank, ThreadBlockRank> metadata,
-    IndexGenerator idx_gen,
+__device__ __forceinline__ void generator_kernel_body(
+    F& f,
+    sclx::kernel_info<IndexGenerator::range_rank, ThreadBlockRank>& metadata,
+    IndexGenerator& idx_gen,
     sclx::index_t slice_idx,
     sclx::index_t slice_size
 ) {
@@ -94,6 +97,23 @@ __global__ void sclx_kernel(
         advance_index(gen_idx, step, global_range);
         metadata.increment_stride_count();
     }
+}
+
+template<class F, uint RangeRank, uint ThreadBlockRank>
+__global__ void
+sclx_kernel(F f, sclx::kernel_info<RangeRank, ThreadBlockRank> metadata) {
+    range_kernel_body(f, metadata);
+}
+
+template<class F, class IndexGenerator, uint ThreadBlockRank>
+__global__ void sclx_kernel(
+    F f,
+    sclx::kernel_info<IndexGenerator::range_rank, ThreadBlockRank> metadata,
+    IndexGenerator idx_gen,
+    sclx::index_t slice_idx,
+    sclx::index_t slice_size
+) {
+    generator_kernel_body(f, metadata, idx_gen, slice_idx, slice_size);
 }
 
 }  // namespace sclx::detail

@@ -283,4 +283,55 @@ __global__ void fold_rows_contig_kernel(
     }
 }
 
+// *out = fold over i of map(in[i]), seeded with `identity` (count_if, min/max_element).
+// Same structure as reduce_kernel: grid-stride with UNROLL independent loads per thread,
+// block fold, per-CTA partials, last CTA (atomic ticket) folds them in fixed order.
+template<class T, class R, class Map, class Op, int THREADS, int UNROLL>
+__global__ void __launch_bounds__(THREADS) map_reduce_kernel(
+    const T* __restrict__ in,
+    size_t n,
+    R identity,
+    R* __restrict__ out,
+    reduce_workspace_t ws,
+    Map map,
+    Op op
+) {
+    __shared__ R s_red[THREADS / 32];
+    __shared__ bool s_last;
+    R acc[UNROLL];
+#pragma unroll
+    for (int u = 0; u < UNROLL; ++u) acc[u] = identity;
+    const size_t step = size_t(gridDim.x) * THREADS;
+    size_t i          = size_t(blockIdx.x) * THREADS + threadIdx.x;
+    for (; i + (UNROLL - 1) * step < n; i += UNROLL * step) {
+        T v[UNROLL];
+#pragma unroll
+        for (int u = 0; u < UNROLL; ++u) v[u] = in[i + u * step];
+#pragma unroll
+        for (int u = 0; u < UNROLL; ++u) acc[u] = op(acc[u], map(v[u]));
+    }
+    for (; i < n; i += step) acc[0] = op(acc[0], map(in[i]));
+#pragma unroll
+    for (int u = 1; u < UNROLL; ++u) acc[0] = op(acc[0], acc[u]);
+    R block = block_reduce<R, Op, THREADS>(acc[0], op, s_red);
+
+    R* partials = static_cast<R*>(ws.partials);
+    if (threadIdx.x == 0) {
+        partials[blockIdx.x] = block;
+        __threadfence();
+        s_last = (atomicAdd(ws.ticket, 1u) == gridDim.x - 1);
+    }
+    __syncthreads();
+    if (!s_last) return;
+    __threadfence();
+    R a = identity;
+    for (unsigned b = threadIdx.x; b < gridDim.x; b += THREADS) a = op(a, load_cg(partials + b));
+    __syncthreads();
+    a = block_reduce<R, Op, THREADS>(a, op, s_red);
+    if (threadIdx.x == 0) {
+        *out       = a;
+        *ws.ticket = 0;
+    }
+}
+
 }  // namespace sclx::b200

@@ -144,4 +144,36 @@ __global__ void __launch_bounds__(THREADS) gather_kernel(
     }
 }
 
+// out[i] = gen(first + i) for i in [0, n): the elementwise kernel behind transform,
+// elementwise_reduce and assign_array.  `gen` only READS (it returns the value), so a thread
+// gathers UNROLL results from coalesced, independent loads before it issues any store: the
+// bytes in flight per thread are UNROLL times those of a per-element lambda whose store may
+// alias its loads (the limit of the generic range dispatcher).
+template<class R, class Gen, int THREADS, int UNROLL>
+__global__ void __launch_bounds__(THREADS)
+    generate_kernel(R* __restrict__ out, size_t n, size_t first, Gen gen) {
+    const size_t tile = size_t(THREADS) * UNROLL;
+    for (size_t base = size_t(blockIdx.x) * tile; base < n; base += size_t(gridDim.x) * tile) {
+        R v[UNROLL];
+        if (base + tile <= n) {
+#pragma unroll
+            for (int u = 0; u < UNROLL; ++u)
+                v[u] = gen(first + base + size_t(u) * THREADS + threadIdx.x);
+#pragma unroll
+            for (int u = 0; u < UNROLL; ++u) out[base + size_t(u) * THREADS + threadIdx.x] = v[u];
+        } else {
+#pragma unroll
+            for (int u = 0; u < UNROLL; ++u) {
+                const size_t i = base + size_t(u) * THREADS + threadIdx.x;
+                if (i < n) v[u] = gen(first + i);
+            }
+#pragma unroll
+            for (int u = 0; u < UNROLL; ++u) {
+                const size_t i = base + size_t(u) * THREADS + threadIdx.x;
+                if (i < n) out[i] = v[u];
+            }
+        }
+    }
+}
+
 }  // namespace sclx::b200

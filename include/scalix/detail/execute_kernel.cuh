@@ -1,0 +1,273 @@
+// scalix-b200: launch machinery behind kernel_handler::launch.
+//
+// Replaces /root/reference scalix/detail/execute_kernel.cuh:41-581.  Same extension points —
+// detail::default_kernel_tag with the two `execute` member templates and
+// REGISTER_SCALIX_KERNEL_TAG(Tag) stamping a distinctly named kernel pair — but:
+//
+//   * no stream is created or destroyed per launch: every logical device owns ONE persistent
+//     non-blocking stream in the runtime;
+//   * a launch group is ordered after the previous group by EVENTS on the device
+//     (sclx_b200_rt_begin_launch / end_launch) and returns as soon as the kernels are queued;
+//     the future returned by execute_kernel synchronises the streams that were used;
+//   * launches for several devices are issued in parallel by the persistent per-device host
+//     threads (cuda::detail::device_workers) instead of a freshly spawned std::async thread;
+//   * grids are sized to the machine (launch_config.cuh); launch errors are checked at once
+//     (the reference only notices them at stream.synchronize()).
+#pragma once
+
+#include "../array.cuh"
+#include "../cuda.hpp"
+#include "../kernel_info.cuh"
+#include "b200/dispatch.cuh"
+#include "b200/launch_config.cuh"
+
+#include <iostream>
+#include <mutex>
+#include <tuple>
+#include <vector>
+
+namespace sclx::detail {
+
+#ifdef SCALIX_DEBUG_KERNEL_LAUNCH
+constexpr bool _debug_kernel_launch = true;
+#else
+constexpr bool _debug_kernel_launch = false;
+#endif
+
+struct _debug_kernel_mutex {
+    static std::mutex& get() {
+        static std::mutex m;
+        return m;
+    }
+};
+
+// logical devices the calling thread has queued work on since execute_kernel started
+struct launch_record {
+    static std::vector<int>& devices() {
+        thread_local std::vector<int> used;
+        return used;
+    }
+    static void note(int device) {
+        auto& used = devices();
+        for (int d : used)
+            if (d == device) return;
+        used.push_back(device);
+    }
+};
+
+using device_info_t = std::vector<std::tuple<int, size_t, size_t>>;
+
+// `issue(ordinal, device_id, slice_idx, slice_size, stream)` queues one kernel; called with
+// the device current, inline for one device, on the device's persistent thread otherwise
+template<class Issue>
+void run_launch_group(const device_info_t& device_info, Issue&& issue) {
+    cuda::detail::ensure_runtime();
+    const int n = int(device_info.size());
+    std::vector<int> devices(n);
+    for (int i = 0; i < n; ++i) devices[i] = std::get<0>(device_info[i]);
+    cuda::detail::check_rt(sclx_b200_rt_begin_launch(n, devices.data()));
+
+    const int caller_device = cuda::traits::current_device();
+    auto issue_one          = [&](int ordinal) {
+        const auto& [device_id, slice_idx, slice_size] = device_info[ordinal];
+        cuda::set_device(device_id);
+        auto stream = static_cast<cudaStream_t>(sclx_b200_rt_stream(device_id));
+        issue(ordinal, device_id, slice_idx, slice_size, stream);
+        cuda::cuda_exception::raise_if_not_success(
+            cudaGetLastError(), std::experimental::source_location::current(), "sclx::detail::"
+        );
+    };
+    if (n == 1) {
+        issue_one(0);
+    } else {
+        std::vector<std::future<void>> issued;
+        issued.reserve(n);
+        for (int i = 0; i < n; ++i)
+            issued.emplace_back(cuda::detail::device_workers::instance().submit(
+                devices[i], [&issue_one, i] { issue_one(i); }
+            ));
+        std::exception_ptr first;
+        for (auto& fut : issued) {
+            try {
+                fut.get();
+            } catch (...) {
+                if (!first) first = std::current_exception();
+            }
+        }
+        if (first) std::rethrow_exception(first);
+    }
+    cuda::set_device(caller_device);
+    cuda::detail::check_rt(sclx_b200_rt_end_launch(n, devices.data()));
+    for (int d : devices) launch_record::note(d);
+}
+
+template<class Kernel>
+void allow_dynamic_shared_memory(Kernel kernel, size_t local_mem_size) {
+    if (local_mem_size <= 48u * 1024u) return;
+    cuda::cuda_exception::raise_if_not_success(
+        cudaFuncSetAttribute(
+            kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, int(local_mem_size)
+        ),
+        std::experimental::source_location::current(),
+        "sclx::detail::"
+    );
+}
+
+// The `execute` pair every kernel tag exposes.  `Kernels` names the __global__ templates:
+//   Kernels::template range<F, RangeRank, TBRank>()          -> kernel pointer
+//   Kernels::template generator<F, IndexGenerator, TBRank>() -> kernel pointer
+template<class Kernels>
+struct tag_executor {
+    // range launch: partition p runs the sub-range whose last coordinate lies in its slice
+    template<uint RangeRank, uint ThreadBlockRank, class F>
+    __host__ static void execute(
+        const device_info_t& device_info,
+        const sclx::md_range_t<RangeRank>& global_range,
+        const sclx::shape_t<ThreadBlockRank>& block_shape,
+        size_t grid_size,
+        size_t local_mem_size,
+        F&& f
+    ) {
+        using functor_t = std::decay_t<F>;
+        auto kernel     = Kernels::template range<functor_t, RangeRank, ThreadBlockRank>();
+        const unsigned block_threads = unsigned(block_shape.elements());
+        std::unique_lock<std::mutex> debug_lock(_debug_kernel_mutex::get(), std::defer_lock);
+        if constexpr (_debug_kernel_launch) {
+            debug_lock.lock();
+            std::cout << "Launching Scalix Kernel" << std::endl;
+        }
+        run_launch_group(
+            device_info,
+            [&](int ordinal, int device_id, size_t slice_idx, size_t slice_size, cudaStream_t stream) {
+                sclx::md_range_t<RangeRank> device_range(global_range);
+                device_range[RangeRank - 1] = slice_size;
+                sclx::md_index_t<RangeRank> device_start_idx{};
+                device_start_idx[RangeRank - 1] = slice_idx;
+                const size_t elements           = device_range.elements();
+                if (elements == 0) return;
+                sclx::kernel_info<RangeRank, ThreadBlockRank> metadata(
+                    global_range, device_range, block_shape, device_start_idx, ordinal
+                );
+                if constexpr (_debug_kernel_launch) {
+                    std::cout << "  Launching kernel on device " << device_id << std::endl;
+                    std::cout << "      Device range: " << device_range << std::endl;
+                    std::cout << "      Device start index: " << device_start_idx << std::endl;
+                    std::cout << "      Global range: " << global_range << std::endl;
+                }
+                (void)device_id;
+                unsigned grid = 1;
+                cuda::cuda_exception::raise_if_not_success(
+                    sclx::b200::range_launch_grid(
+                        kernel, elements, block_threads, local_mem_size, grid_size, &grid,
+                        sclx::cuda::traits::kernel::max_thread_count()
+                    ),
+                    std::experimental::source_location::current(),
+                    "sclx::detail::"
+                );
+                allow_dynamic_shared_memory(kernel, local_mem_size);
+                kernel<<<grid, block_threads, local_mem_size, stream>>>(f, metadata);
+            }
+        );
+        if constexpr (_debug_kernel_launch)
+            std::cout << "Kernel launch complete" << std::endl << std::endl;
+    }
+
+    // index-generator launch: every partition walks the WHOLE generator range and keeps the
+    // indices whose last coordinate it owns (replicated execution with owner filter)
+    template<class IndexGenerator, uint ThreadBlockRank, class F>
+    __host__ static void execute(
+        const device_info_t& device_info,
+        IndexGenerator&& index_generator,
+        const sclx::shape_t<ThreadBlockRank>& block_shape,
+        size_t grid_size,
+        size_t local_mem_size,
+        F&& f
+    ) {
+        using functor_t   = std::decay_t<F>;
+        using generator_t = std::decay_t<IndexGenerator>;
+        constexpr uint range_rank = generator_t::range_rank;
+        auto kernel = Kernels::template generator<functor_t, generator_t, ThreadBlockRank>();
+        const unsigned block_threads = unsigned(block_shape.elements());
+        std::unique_lock<std::mutex> debug_lock(_debug_kernel_mutex::get(), std::defer_lock);
+        if constexpr (_debug_kernel_launch) {
+            debug_lock.lock();
+            std::cout << "Launching Scalix Kernel using IndexGenerator" << std::endl;
+        }
+        const auto generator_range = index_generator.range();
+        run_launch_group(
+            device_info,
+            [&](int ordinal, int device_id, size_t slice_idx, size_t slice_size, cudaStream_t stream) {
+                const size_t elements = generator_range.elements();
+                if (elements == 0 || slice_size == 0) return;
+                sclx::kernel_info<range_rank, ThreadBlockRank> metadata(
+                    generator_range, generator_range, block_shape, {}, ordinal
+                );
+                if constexpr (_debug_kernel_launch) {
+                    std::cout << "  Launching kernel on device " << device_id << std::endl;
+                    std::cout << "      Device slice size: " << slice_size << std::endl;
+                    std::cout << "      Device slice start index: " << slice_idx << std::endl;
+                }
+                (void)device_id;
+                unsigned grid = 1;
+                cuda::cuda_exception::raise_if_not_success(
+                    sclx::b200::range_launch_grid(
+                        kernel, elements, block_threads, local_mem_size, grid_size, &grid,
+                        sclx::cuda::traits::kernel::max_thread_count()
+                    ),
+                    std::experimental::source_location::current(),
+                    "sclx::detail::"
+                );
+                allow_dynamic_shared_memory(kernel, local_mem_size);
+                kernel<<<grid, block_threads, local_mem_size, stream>>>(
+                    f, metadata, index_generator, slice_idx, slice_size
+                );
+            }
+        );
+        if constexpr (_debug_kernel_launch)
+            std::cout << "Kernel launch complete" << std::endl << std::endl;
+    }
+};
+
+struct default_kernels {
+    template<class F, uint RangeRank, uint ThreadBlockRank>
+    static auto range() {
+        return &sclx_kernel<F, RangeRank, ThreadBlockRank>;
+    }
+    template<class F, class IndexGenerator, uint ThreadBlockRank>
+    static auto generator() {
+        return &sclx_kernel<F, IndexGenerator, ThreadBlockRank>;
+    }
+};
+
+struct default_kernel_tag : tag_executor<default_kernels> {};
+
+}  // namespace sclx::detail
+
+// Stamps `sclx_<Tag>` kernels (so profilers show a distinct name per tag) and a struct `Tag`
+// with the default_kernel_tag interface; use as `handler.launch<Tag>(...)`.
+#define REGISTER_SCALIX_KERNEL_TAG(Tag)                                                          \
+    template<class F, uint RangeRank, uint ThreadBlockRank>                                      \
+    __global__ void sclx_##Tag(F f, sclx::kernel_info<RangeRank, ThreadBlockRank> metadata) {    \
+        sclx::detail::range_kernel_body(f, metadata);                                            \
+    }                                                                                            \
+    template<class F, class IndexGenerator, uint ThreadBlockRank>                                \
+    __global__ void sclx_##Tag(                                                                  \
+        F f,                                                                                     \
+        sclx::kernel_info<IndexGenerator::range_rank, ThreadBlockRank> metadata,                 \
+        IndexGenerator idx_gen,                                                                  \
+        sclx::index_t slice_idx,                                                                 \
+        sclx::index_t slice_size                                                                 \
+    ) {                                                                                          \
+        sclx::detail::generator_kernel_body(f, metadata, idx_gen, slice_idx, slice_size);        \
+    }                                                                                            \
+    struct Tag##_sclx_kernels {                                                                  \
+        template<class F, uint RangeRank, uint ThreadBlockRank>                                  \
+        static auto range() {                                                                    \
+            return &sclx_##Tag<F, RangeRank, ThreadBlockRank>;                                   \
+        }                                                                                        \
+        template<class F, class IndexGenerator, uint ThreadBlockRank>                            \
+        static auto generator() {                                                                \
+            return &sclx_##Tag<F, IndexGenerator, ThreadBlockRank>;                              \
+        }                                                                                        \
+    };                                                                                           \
+    struct Tag : sclx::detail::tag_executor<Tag##_sclx_kernels> {}

@@ -1,0 +1,395 @@
+// scalix-b200: sclx::execute_kernel, kernel_handler and local_array.
+//
+// Public surface of /root/reference scalix/execute_kernel.cuh:45-515.  What changes underneath
+// (BASELINE.json north_star, subsystem 2):
+//
+//   reference : execute_kernel spawns a std::async thread per call; launch creates one stream
+//               per device, toggles cudaMemAdvise(ReadMostly) on every result array twice
+//               and blocks until all streams are idle (ibid. :286,300-302,506-513).
+//   here      : the host lambda runs at once on the calling thread and only QUEUES kernels on
+//               the persistent per-device streams; ordering between consecutive launches is
+//               kept on the device with events; the returned std::future<void> synchronises
+//               the streams that were used when it is waited on.  Anything that reads results
+//               on the host (array::operator[] through the mirror, algorithm return values)
+//               synchronises by itself, so a dropped future is harmless.
+#pragma once
+
+#include "array.cuh"
+#include "array_list.cuh"
+#include "array_tuple.cuh"
+#include "cuda.hpp"
+#include "detail/execute_kernel.cuh"
+#include "kernel_info.cuh"
+#include "range.cuh"
+#include "shape.cuh"
+
+#include <future>
+
+namespace sclx {
+
+class kernel_handler {
+  public:
+    // ---- range launches ---------------------------------------------------------------
+    template<
+        class KernelTag = detail::default_kernel_tag,
+        uint RangeRank,
+        class T,
+        uint ResultRank,
+        uint NResult,
+        class F,
+        uint ThreadBlockRank = cuda::traits::kernel::default_block_shape.rank()>
+    __host__ void launch(
+        md_range_t<RangeRank> range,
+        array_list<T, ResultRank, NResult> result,
+        F&& f,
+        shape_t<ThreadBlockRank> block_shape = cuda::traits::kernel::default_block_shape,
+        size_t grid_size                     = cuda::traits::kernel::default_grid_size
+    ) const {
+        launch_array_list_impl<KernelTag>(range, result, block_shape, grid_size, std::forward<F>(f));
+    }
+
+    template<
+        class KernelTag = detail::default_kernel_tag,
+        uint RangeRank,
+        class T,
+        uint ResultRank,
+        class F,
+        uint ThreadBlockRank = cuda::traits::kernel::default_block_shape.rank()>
+    __host__ void launch(
+        md_range_t<RangeRank> range,
+        dynamic_array_list<T, ResultRank> result,
+        F&& f,
+        shape_t<ThreadBlockRank> block_shape = cuda::traits::kernel::default_block_shape,
+        size_t grid_size                     = cuda::traits::kernel::default_grid_size
+    ) const {
+        launch_array_list_impl<KernelTag>(range, result, block_shape, grid_size, std::forward<F>(f));
+    }
+
+    template<
+        class KernelTag = detail::default_kernel_tag,
+        uint RangeRank,
+        class T,
+        uint ResultRank,
+        class F,
+        uint ThreadBlockRank = cuda::traits::kernel::default_block_shape.rank()>
+    __host__ void launch(
+        md_range_t<RangeRank> range,
+        array<T, ResultRank> result,
+        F&& f,
+        shape_t<ThreadBlockRank> block_shape = cuda::traits::kernel::default_block_shape,
+        size_t grid_size                     = cuda::traits::kernel::default_grid_size
+    ) const {
+        launch<KernelTag>(
+            range, array_list<T, ResultRank, 1>({result}), std::forward<F>(f), block_shape, grid_size
+        );
+    }
+
+    template<
+        class KernelTag = detail::default_kernel_tag,
+        uint RangeRank,
+        class F,
+        uint ThreadBlockRank = cuda::traits::kernel::default_block_shape.rank(),
+        class... ArrayTypes>
+    __host__ void launch(
+        md_range_t<RangeRank> range,
+        array_tuple<ArrayTypes...> result,
+        F&& f,
+        shape_t<ThreadBlockRank> block_shape = cuda::traits::kernel::default_block_shape,
+        size_t grid_size                     = cuda::traits::kernel::default_grid_size
+    ) const {
+        launch_tuple_impl<KernelTag>(range, result, block_shape, grid_size, std::forward<F>(f));
+    }
+
+    // ---- index-generator launches -------------------------------------------------------
+    template<
+        class KernelTag = detail::default_kernel_tag,
+        class IndexGenerator,
+        class T,
+        uint ResultRank,
+        uint NResult,
+        class F,
+        uint ThreadBlockRank = cuda::traits::kernel::default_block_shape.rank()>
+    __host__ void launch(
+        IndexGenerator&& index_generator,
+        array_list<T, ResultRank, NResult> result,
+        F&& f,
+        shape_t<ThreadBlockRank> block_shape = cuda::traits::kernel::default_block_shape,
+        size_t grid_size                     = cuda::traits::kernel::default_grid_size
+    ) const {
+        launch_array_list_impl<KernelTag>(
+            std::forward<IndexGenerator>(index_generator), result, block_shape, grid_size,
+            std::forward<F>(f)
+        );
+    }
+
+    template<
+        class KernelTag = detail::default_kernel_tag,
+        class IndexGenerator,
+        class T,
+        uint ResultRank,
+        class F,
+        uint ThreadBlockRank = cuda::traits::kernel::default_block_shape.rank()>
+    __host__ void launch(
+        IndexGenerator&& index_generator,
+        dynamic_array_list<T, ResultRank> result,
+        F&& f,
+        shape_t<ThreadBlockRank> block_shape = cuda::traits::kernel::default_block_shape,
+        size_t grid_size                     = cuda::traits::kernel::default_grid_size
+    ) const {
+        launch_array_list_impl<KernelTag>(
+            std::forward<IndexGenerator>(index_generator), result, block_shape, grid_size,
+            std::forward<F>(f)
+        );
+    }
+
+    template<
+        class KernelTag = detail::default_kernel_tag,
+        class IndexGenerator,
+        class T,
+        uint ResultRank,
+        class F,
+        uint ThreadBlockRank = cuda::traits::kernel::default_block_shape.rank()>
+    __host__ void launch(
+        IndexGenerator&& index_generator,
+        array<T, ResultRank> result,
+        F&& f,
+        shape_t<ThreadBlockRank> block_shape = cuda::traits::kernel::default_block_shape,
+        size_t grid_size                     = cuda::traits::kernel::default_grid_size
+    ) const {
+        launch<KernelTag>(
+            std::forward<IndexGenerator>(index_generator),
+            array_list<T, ResultRank, 1>({result}),
+            std::forward<F>(f),
+            block_shape,
+            grid_size
+        );
+    }
+
+    template<
+        class KernelTag = detail::default_kernel_tag,
+        class IndexGenerator,
+        class F,
+        uint ThreadBlockRank = cuda::traits::kernel::default_block_shape.rank(),
+        class... ArrayTypes>
+    __host__ void launch(
+        IndexGenerator&& index_generator,
+        array_tuple<ArrayTypes...> result,
+        F&& f,
+        shape_t<ThreadBlockRank> block_shape = cuda::traits::kernel::default_block_shape,
+        size_t grid_size                     = cuda::traits::kernel::default_grid_size
+    ) const {
+        launch_tuple_impl<KernelTag>(
+            std::forward<IndexGenerator>(index_generator), result, block_shape, grid_size,
+            std::forward<F>(f)
+        );
+    }
+
+    // usable inside device lambdas that captured the handler by value
+    __device__ void syncthreads() const { __syncthreads(); }
+    __device__ void threadfence() const { __threadfence(); }
+
+    template<class T, uint Rank>
+    friend class local_array;
+
+  private:
+    __device__ static char* get_local_mem(const size_t& offset) {
+        extern __shared__ char local_mem[];
+        return local_mem + offset;
+    }
+
+    // every result array must be partitioned like the first one
+    template<class ArrayListType>
+    __host__ static auto unify_split(ArrayListType& result) {
+        auto device_split_first = get_device_split_info(result[0]);
+        for (auto& array : result) {
+            if (!is_same_device_split(device_split_first, get_device_split_info(array))) {
+                array.set_primary_devices(device_split_first);
+                std::cerr << "Warning: Not every array in the list has the same "
+                             "memory split, setting primary devices for all "
+                             "arrays to the same as the first array in the list"
+                          << std::endl;
+            }
+        }
+        return get_device_split_info(result[0]);
+    }
+
+    template<class KernelTag, uint RangeRank, uint ThreadBlockRank, class ArrayListType, class F>
+    __host__ void launch_array_list_impl(
+        md_range_t<RangeRank> range,
+        ArrayListType&& result,
+        shape_t<ThreadBlockRank> block_shape,
+        size_t grid_size,
+        F&& f
+    ) const {
+        const size_t last_dim = result[0].shape()[result[0].rank() - 1];
+        for (auto& array : result) {
+            if (array.shape()[array.rank() - 1] != last_dim) {
+                throw_exception<std::invalid_argument>(
+                    "All arrays in the result must have the same last dimension"
+                );
+            }
+        }
+        auto device_info = unify_split(result);
+        KernelTag::template execute<RangeRank, ThreadBlockRank>(
+            device_info, range, block_shape, grid_size, local_mem_size_, std::forward<F>(f)
+        );
+    }
+
+    template<
+        class KernelTag,
+        class IndexGenerator,
+        uint ThreadBlockRank,
+        class ArrayListType,
+        class F,
+        class = std::void_t<decltype(std::decay_t<IndexGenerator>::index_rank)>>
+    __host__ void launch_array_list_impl(
+        IndexGenerator&& index_generator,
+        ArrayListType&& result,
+        shape_t<ThreadBlockRank> block_shape,
+        size_t grid_size,
+        F&& f
+    ) const {
+        using generator_t = std::remove_reference_t<IndexGenerator>;
+        for (auto& array : result) {
+            if (index_generator.index_range()[generator_t::index_rank - 1]
+                != array.shape()[array.rank() - 1]) {
+                throw std::invalid_argument("Index generator indices and "
+                                            "result array must have the same "
+                                            "last dimension");
+            }
+        }
+        auto device_info = unify_split(result);
+        KernelTag::template execute<IndexGenerator, ThreadBlockRank>(
+            device_info, index_generator, block_shape, grid_size, local_mem_size_,
+            std::forward<F>(f)
+        );
+    }
+
+    template<class KernelTag, uint RangeRank, uint ThreadBlockRank, class F, class... ArrayTypes>
+    __host__ void launch_tuple_impl(
+        md_range_t<RangeRank> range,
+        array_tuple<ArrayTypes...> result,
+        shape_t<ThreadBlockRank> block_shape,
+        size_t grid_size,
+        F&& f
+    ) const {
+        if (!result.last_dims_all_equal()) {
+            throw_exception<std::invalid_argument>(
+                "All arrays in the result must have the same last dimension"
+            );
+        }
+        auto device_info = get_device_split_info(
+            thrust::get<0>(static_cast<thrust::tuple<ArrayTypes...>&>(result))
+        );
+        KernelTag::template execute<RangeRank, ThreadBlockRank>(
+            device_info, range, block_shape, grid_size, local_mem_size_, std::forward<F>(f)
+        );
+    }
+
+    template<
+        class KernelTag,
+        class IndexGenerator,
+        uint ThreadBlockRank,
+        class F,
+        class... ArrayTypes,
+        class = std::void_t<decltype(std::decay_t<IndexGenerator>::index_rank)>>
+    __host__ void launch_tuple_impl(
+        IndexGenerator&& index_generator,
+        array_tuple<ArrayTypes...> result,
+        shape_t<ThreadBlockRank> block_shape,
+        size_t grid_size,
+        F&& f
+    ) const {
+        using generator_t = std::remove_reference_t<IndexGenerator>;
+        auto& first = thrust::get<0>(static_cast<thrust::tuple<ArrayTypes...>&>(result));
+        if (index_generator.index_range()[generator_t::index_rank - 1]
+            != first.trailing_dimension()) {
+            throw_exception<std::invalid_argument>(
+                "Index generator indices and result array must have the same last dimension"
+            );
+        }
+        if (!result.last_dims_all_equal()) {
+            throw_exception<std::invalid_argument>(
+                "All arrays in the result must have the same last dimension"
+            );
+        }
+        auto device_info = get_device_split_info(first);
+        KernelTag::template execute<IndexGenerator, ThreadBlockRank>(
+            device_info, index_generator, block_shape, grid_size, local_mem_size_,
+            std::forward<F>(f)
+        );
+    }
+
+    size_t local_mem_size_ = 0;  // dynamic shared memory requested by local_arrays
+};
+
+// A view of the launch's dynamic shared memory.  Construct it on the host inside the
+// execute_kernel lambda (this reserves the bytes), capture it BY VALUE into a `mutable`
+// device lambda.
+template<class T, uint Rank>
+class local_array {
+  public:
+    local_array() = default;
+
+    __host__ local_array(kernel_handler& handler, const shape_t<Rank>& shape) : shape_(shape) {
+        const size_t misalign = handler.local_mem_size_ % alignof(T);
+        if (misalign != 0) handler.local_mem_size_ += alignof(T) - misalign;
+        offset_ = handler.local_mem_size_;
+        handler.local_mem_size_ += elements() * sizeof(T);
+    }
+
+    __device__ T& operator[](const md_index_t<Rank>& idx) { return data()[idx.as_linear(shape_)]; }
+
+    __device__ T& operator[](const index_t& idx) { return data()[idx]; }
+
+    template<class... Args>
+    __device__ T& operator()(const Args&... args) {
+        return operator[](md_index_t<Rank>{static_cast<const size_t&>(args)...});
+    }
+
+    __host__ __device__ size_t elements() const { return shape_.elements(); }
+
+    __host__ __device__ const shape_t<Rank>& shape() const { return shape_; }
+
+    __device__ T* data() {
+        if (!data_) data_ = reinterpret_cast<T*>(kernel_handler::get_local_mem(offset_));
+        return data_;
+    }
+
+    __device__ T* begin() { return data(); }
+
+    __device__ T* end() { return begin() + elements(); }
+
+  private:
+    size_t offset_{};
+    shape_t<Rank> shape_;
+    T* data_{};  // resolved on first use inside the kernel
+};
+
+// Runs `f(handler)` now (it queues kernels, it does not wait for them) and returns a future
+// that completes when everything it queued has finished.  Exceptions thrown by `f` and CUDA
+// errors of the queued work are delivered by future::get(), like the reference's.
+template<class F>
+__host__ std::future<void> execute_kernel(F&& f) {
+    cuda::detail::ensure_runtime();
+    auto& used = detail::launch_record::devices();
+    const std::vector<int> outer(std::move(used));  // nested execute_kernel calls
+    used.clear();
+    std::exception_ptr error;
+    try {
+        kernel_handler handler;
+        f(handler);
+    } catch (...) {
+        error = std::current_exception();
+    }
+    std::vector<int> devices = used;
+    used                     = outer;
+    for (int d : devices) detail::launch_record::note(d);
+    return std::async(std::launch::deferred, [devices = std::move(devices), error]() {
+        if (error) std::rethrow_exception(error);
+        if (!devices.empty())
+            cuda::detail::check_rt(sclx_b200_rt_sync_devices(int(devices.size()), devices.data()));
+    });
+}
+
+}  // namespace sclx

@@ -207,6 +207,7 @@ int sclx_b200_rt_sync_devices(int ndev, const int* devices);
 
 /* per-device workspaces of the scan / reduce kernels (valid in stream order on that device) */
 int sclx_b200_rt_scan_workspace(int logical, size_t tiles, void** desc, unsigned* epoch);
+int sclx_b200_rt_scan_counters(int logical, void** counters);
 int sclx_b200_rt_reduce_workspace(int logical, size_t bytes, void** partials, void** ticket);
 int sclx_b200_rt_scratch(size_t bytes, void** ptr); /* small peer-visible scratch */
 

@@ -82,6 +82,7 @@ ABI = {
     "sclx_b200_rt_stream_wait": (_i, [_i, _i]),
     "sclx_b200_rt_sync_devices": (_i, [_i, _vp]),
     "sclx_b200_rt_scan_workspace": (_i, [_i, _sz, _pp, _vp]),
+    "sclx_b200_rt_scan_counters": (_i, [_i, _pp]),
     "sclx_b200_rt_reduce_workspace": (_i, [_i, _sz, _pp, _pp]),
     "sclx_b200_rt_scratch": (_i, [_sz, _pp]),
 }

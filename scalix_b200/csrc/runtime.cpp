@@ -434,7 +434,13 @@ int map_runs(allocation& al, bool zero) {
             RT(cudaSetDevice(ld.physical));
             RT(cudaMemsetAsync(al.base + r.offset, 0, r.bytes, ld.stream));
         }
-        g_rt.unsynced.store(true);
+        // the caller may touch the memory from ANY stream (thrust on raw pointers, cudaMemcpy)
+        // right after creation: the zero-fill must not still be in flight
+        for (auto& r : al.runs) {
+            logical_device& ld = g_rt.dev[r.logical_device];
+            RT(cudaSetDevice(ld.physical));
+            RT(cudaStreamSynchronize(ld.stream));
+        }
     }
     RT(cudaSetDevice(cur));
     return 0;
@@ -742,6 +748,15 @@ int sclx_b200_rt_scan_workspace(int logical, size_t tiles, void** desc, unsigned
     RT(cudaSetDevice(cur));
     *desc  = ld.scan_desc;
     *epoch = ld.scan_epoch;
+    return 0;
+}
+
+// tile-ticket counters of the streaming scan (zero-initialised, self-resetting)
+int sclx_b200_rt_scan_counters(int logical, void** counters) {
+    if (int rc = ensure_init()) return rc;
+    if (logical < 0 || logical >= (int)g_rt.dev.size() || !counters)
+        return fail(SCLX_E_INVALID_ARGUMENT, "bad device");
+    *counters = g_rt.dev[logical].ticket + 32;
     return 0;
 }
 
