@@ -23,6 +23,7 @@
 
 #include "cuda.hpp"
 #include "index.cuh"
+#include "range.cuh"
 #include "shape.cuh"
 #include "throw_exception.hpp"
 
