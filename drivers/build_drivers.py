@@ -1,0 +1,60 @@
+"""Builds the header-API programs against include/ (sm_100a) into drivers/bin/:
+   parity_driver_ours  — drivers/parity_driver.cu (public sclx:: API only)
+   ex_<name>           — the reference's five examples, compiled UNMODIFIED from
+                         /root/reference/examples (only when that tree is present; nothing is
+                         copied into this repository, the binaries are git-ignored)
+Called by __graft_entry__.build()."""
+import os
+import subprocess
+import sys
+from concurrent.futures import ThreadPoolExecutor
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+REPO = os.path.dirname(HERE)
+BIN = os.path.join(HERE, "bin")
+LIBDIR = os.path.join(REPO, "scalix_b200", "lib")
+REF_EXAMPLES = "/root/reference/examples"
+EXAMPLES = ["inclusive_scan", "reduce_last_dim", "index_generator", "distributed_indexing", "scaling_performance"]
+FLAGS = ["-std=c++17", "-O3", "-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "--extended-lambda",
+         "--expt-relaxed-constexpr", "-Xcudafe", "--diag_suppress=177", "-I", os.path.join(REPO, "include"),
+         "-L", LIBDIR, "-lscalix_b200", "-Xlinker", "-rpath", "-Xlinker", "$ORIGIN/../../scalix_b200/lib"]
+
+
+def newest_header():
+    newest = 0.0
+    for root, _, files in os.walk(os.path.join(REPO, "include")):
+        for f in files:
+            newest = max(newest, os.path.getmtime(os.path.join(root, f)))
+    return newest
+
+
+def build_one(src, out, extra=()):
+    if os.path.exists(out) and os.path.getmtime(out) >= max(os.path.getmtime(src), newest_header()):
+        return out, 0, ""
+    p = subprocess.run(["nvcc", *FLAGS, *extra, "-o", out, src], capture_output=True, text=True)
+    return out, p.returncode, p.stdout + p.stderr
+
+
+def main(force=False):
+    os.makedirs(BIN, exist_ok=True)
+    jobs = [(os.path.join(HERE, "parity_driver.cu"), os.path.join(BIN, "parity_driver_ours"), ())]
+    if os.path.isdir(REF_EXAMPLES):
+        for ex in EXAMPLES:
+            jobs.append((os.path.join(REF_EXAMPLES, ex + ".cu"), os.path.join(BIN, "ex_" + ex), ("-I", REF_EXAMPLES)))
+    if force:
+        for _, out, _ in jobs:
+            if os.path.exists(out):
+                os.remove(out)
+    failed = []
+    with ThreadPoolExecutor(max_workers=6) as pool:
+        for out, rc, log in pool.map(lambda j: build_one(*j), jobs):
+            if rc != 0:
+                failed.append((out, log))
+    for out, log in failed:
+        sys.stderr.write(f"FAILED {out}\n{log[-4000:]}\n")
+    if failed:
+        raise SystemExit(1)
+
+
+if __name__ == "__main__":
+    main(force="--force" in sys.argv)

@@ -1,0 +1,238 @@
+// parity_driver — one source, two builds:
+//   drivers/bin/parity_driver_ours   compiled against include/            (this repository)
+//   oracle/_ref/parity_driver_ref    compiled against /root/reference     (the UNMODIFIED
+//                                    reference headers, Unified-Memory build; oracle/Makefile)
+// It uses ONLY the public sclx:: API, so both builds run the same program.  tests/ run both on
+// the GPU box and compare the dumped outputs (bit-exact for integer work, 1e-5 relative for
+// float sums); bench.py --impl reference times the reference build with the bench_* commands.
+//
+//   parity_driver dump  <case> <n> <outfile>          run a parity case, dump raw result bytes
+//   parity_driver bench <case> <n> <steps> <warmup>   print {"ms_per_step": ..} (wall clock
+//                                                      around the blocking public API call)
+// cases: scan_i32 scan_i64 rld_f32 rld_u32max axpy_f32 axpy_f32_r3 gather_f32 fill_iota
+#include <scalix/algorithm/inclusive_scan.cuh>
+#include <scalix/algorithm/reduce.cuh>
+#include <scalix/algorithm/reduce_last_dim.cuh>
+#include <scalix/fill.cuh>
+#include <scalix/iota.cuh>
+#include <scalix/scalix.cuh>
+
+#include <chrono>
+#include <cstdio>
+#include <cstdlib>
+#include <cstring>
+#include <string>
+#include <vector>
+
+// same generator as oracle/scalix_oracle.c (oracle_splitmix64): value for (seed, index)
+__host__ __device__ inline unsigned long long splitmix64(unsigned long long seed, unsigned long long i) {
+    unsigned long long z = seed + (i + 1) * 0x9E3779B97F4A7C15ull;
+    z = (z ^ (z >> 30)) * 0xBF58476D1CE4E5B9ull;
+    z = (z ^ (z >> 27)) * 0x94D049BB133111EBull;
+    return z ^ (z >> 31);
+}
+__host__ __device__ inline float uniform01(unsigned long long seed, unsigned long long i) {
+    return float(splitmix64(seed, i) >> 40) * (1.0f / 16777216.0f);
+}
+__host__ __device__ inline float symmetric(unsigned long long seed, unsigned long long i) {
+    return uniform01(seed, i) * 2.0f - 1.0f;
+}
+
+template<class T, uint Rank, class Gen>
+void generate(sclx::array<T, Rank>& arr, Gen gen) {
+    const auto shape = arr.shape();
+    sclx::execute_kernel([&](sclx::kernel_handler& handler) {
+        handler.launch(
+            sclx::md_range_t<Rank>(shape),
+            arr,
+            [=] __device__(const sclx::md_index_t<Rank>& idx, const auto&) {
+                arr[idx] = gen(idx.as_linear(shape));
+            }
+        );
+    }).get();
+}
+
+template<class T, uint Rank>
+int dump(const sclx::array<T, Rank>& arr, const char* path) {
+    std::vector<T> host(arr.elements());
+    cudaDeviceSynchronize();
+    if (cudaMemcpy(host.data(), arr.data().get(), sizeof(T) * host.size(), cudaMemcpyDefault) != cudaSuccess) {
+        std::fprintf(stderr, "dump: cudaMemcpy failed\n");
+        return 3;
+    }
+    FILE* f = std::fopen(path, "wb");
+    if (!f) return 4;
+    std::fwrite(host.data(), sizeof(T), host.size(), f);
+    std::fclose(f);
+    return 0;
+}
+
+struct timer {
+    std::chrono::steady_clock::time_point t0 = std::chrono::steady_clock::now();
+    double ms() const {
+        return std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t0).count();
+    }
+};
+
+template<class Step>
+int bench(Step&& step, int steps, int warmup) {
+    for (int i = 0; i < warmup; ++i) step();
+    cudaDeviceSynchronize();
+    timer t;
+    for (int i = 0; i < steps; ++i) step();
+    cudaDeviceSynchronize();
+    std::printf("{\"ms_per_step\": %.6f, \"steps\": %d, \"warmup\": %d}\n", t.ms() / steps, steps, warmup);
+    return 0;
+}
+
+// ---- cases --------------------------------------------------------------------------------
+// every case: build inputs with the public API, run the public API call under test; `out`
+// receives the array to dump; `step` re-runs only the call under test (for bench)
+
+int run_case(const std::string& what, const std::string& name, size_t n, const char* path, int steps, int warmup) {
+    const bool do_dump = what == "dump";
+    if (name == "scan_i32") {
+        // BASELINE.json configs[0] with the wrap-around start of BASELINE.md
+        sclx::array<int, 1> a({n});
+        sclx::iota(a, 0x7FFF0000);
+        sclx::array<int, 1> r({n});
+        auto step = [&] { sclx::algorithm::inclusive_scan(a, r, 0, sclx::algorithm::plus<>()); };
+        step();
+        return do_dump ? dump(r, path) : bench(step, steps, warmup);
+    }
+    if (name == "scan_i64") {
+        // configs[4] data: SplitMix64 & 0xFFFF, rank-3 storage {2, 2, n/4} scanned flattened
+        sclx::array<long long, 3> a({2, 2, n / 4});
+        generate(a, [] __device__(size_t i) { return (long long)(splitmix64(0x5CA5, i) & 0xFFFF); });
+        sclx::array<long long, 3> r({2, 2, n / 4});
+        auto step = [&] { sclx::algorithm::inclusive_scan(a, r, 0ll, sclx::algorithm::plus<>()); };
+        step();
+        return do_dump ? dump(r, path) : bench(step, steps, warmup);
+    }
+    if (name == "rld_f32") {
+        // configs[1]: float32 [64, n] sum along the last dimension
+        sclx::array<float, 2> a({64, n});
+        generate(a, [] __device__(size_t i) { return uniform01(0x5CA11, i); });
+        sclx::array<float, 1> r({64});
+        auto step = [&] { sclx::algorithm::reduce_last_dim(a, r, 0.f, sclx::algorithm::plus<>()); };
+        step();
+        return do_dump ? dump(r, path) : bench(step, steps, warmup);
+    }
+    if (name == "rld_u32max") {
+        // the reference example's check (examples/reduce_last_dim.cu:55-84) on {3,3,3,n}
+        sclx::array<unsigned, 4> a({3, 3, 3, n});
+        sclx::execute_kernel([&](sclx::kernel_handler& handler) {
+            handler.launch(
+                sclx::md_range_t<4>{a.shape()},
+                a,
+                [=] __device__(const sclx::md_index_t<4>& index, const auto&) {
+                    a[index] = unsigned(splitmix64(index[3], 7) % 1000003u) + unsigned(index[0]);
+                }
+            );
+        }).get();
+        sclx::array<unsigned, 3> r({3, 3, 3});
+        auto step = [&] { sclx::algorithm::reduce_last_dim(a, r, 0u, sclx::algorithm::max<>()); };
+        step();
+        return do_dump ? dump(r, path) : bench(step, steps, warmup);
+    }
+    if (name == "axpy_f32") {
+        // configs[2]: y = a*x + y through a user lambda on execute_kernel
+        sclx::array<float, 1> x({n}), y({n});
+        generate(x, [] __device__(size_t i) { return symmetric(1, i); });
+        generate(y, [] __device__(size_t i) { return symmetric(2, i); });
+        const float alpha = 1.5f;
+        auto step = [&] {
+            sclx::execute_kernel([&](sclx::kernel_handler& handler) {
+                handler.launch(
+                    sclx::md_range_t<1>{y.shape()},
+                    y,
+                    [=] __device__(const sclx::md_index_t<1>& idx, const auto&) {
+                        y[idx] = alpha * x[idx] + y[idx];
+                    }
+                );
+            }).get();
+        };
+        step();
+        return do_dump ? dump(y, path) : bench(step, steps, warmup);
+    }
+    if (name == "axpy_f32_r3") {
+        sclx::array<float, 3> x({4, 4, n / 16}), y({4, 4, n / 16});
+        generate(x, [] __device__(size_t i) { return symmetric(3, i); });
+        generate(y, [] __device__(size_t i) { return symmetric(4, i); });
+        const float alpha = -0.75f;
+        auto step = [&] {
+            sclx::execute_kernel([&](sclx::kernel_handler& handler) {
+                handler.launch(
+                    sclx::md_range_t<3>{y.shape()},
+                    y,
+                    [=] __device__(const sclx::md_index_t<3>& idx, const auto&) {
+                        y[idx] = alpha * x[idx] + y[idx];
+                    }
+                );
+            }).get();
+        };
+        step();
+        return do_dump ? dump(y, path) : bench(step, steps, warmup);
+    }
+    if (name == "gather_f32") {
+        // configs[3]: out[i] = src[index[i]], n indices into a 4n-element source
+        sclx::array<float, 1> src({4 * n}), out({n});
+        sclx::array<size_t, 1> index({n});
+        const size_t m = 4 * n;
+        generate(src, [] __device__(size_t i) { return uniform01(0xABC, i); });
+        generate(index, [=] __device__(size_t i) { return size_t(splitmix64(0x6A7, i) % m); });
+        auto step = [&] {
+            sclx::execute_kernel([&](sclx::kernel_handler& handler) {
+                handler.launch(
+                    sclx::md_range_t<1>{out.shape()},
+                    out,
+                    [=] __device__(const sclx::md_index_t<1>& idx, const auto&) {
+                        out[idx] = src[index[idx]];
+                    }
+                );
+            }).get();
+        };
+        step();
+        return do_dump ? dump(out, path) : bench(step, steps, warmup);
+    }
+    if (name == "fill_iota") {
+        // fill a rank-3 array, iota a rank-1 array, add them element-wise through a lambda
+        sclx::array<int, 3> f({4, 4, n / 16});
+        sclx::array<int, 1> io({n});
+        auto step = [&] {
+            sclx::fill(f, 41);
+            sclx::iota(io, 1);
+        };
+        step();
+        sclx::array<int, 1> r({n});
+        sclx::execute_kernel([&](sclx::kernel_handler& handler) {
+            handler.launch(
+                sclx::md_range_t<1>{r.shape()},
+                r,
+                [=] __device__(const sclx::md_index_t<1>& idx, const auto&) {
+                    r[idx] = f[idx[0]] + io[idx];
+                }
+            );
+        }).get();
+        return do_dump ? dump(r, path) : bench(step, steps, warmup);
+    }
+    std::fprintf(stderr, "unknown case %s\n", name.c_str());
+    return 2;
+}
+
+int main(int argc, char** argv) {
+    if (argc < 5) {
+        std::fprintf(stderr, "usage: %s dump <case> <n> <outfile> | bench <case> <n> <steps> <warmup>\n", argv[0]);
+        return 2;
+    }
+    const std::string what = argv[1], name = argv[2];
+    const size_t n = std::strtoull(argv[3], nullptr, 10);
+    try {
+        if (what == "dump") return run_case(what, name, n, argv[4], 0, 0);
+        if (what == "bench") return run_case(what, name, n, nullptr, std::atoi(argv[4]), argc > 5 ? std::atoi(argv[5]) : 3);
+    } catch (const std::exception& e) {
+        std::fprintf(stderr, "parity_driver: %s\n", e.what());
+        return 1;
+    }
+    return 2;
+}

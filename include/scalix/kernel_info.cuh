@@ -50,8 +50,14 @@ class kernel_info {
     }
     __device__ index_t local_thread_linear_id() const { return threadIdx.x; }
 
+    // Linear index (in global_range) of the element this thread is working on.  The
+    // reference launches one thread per element, so its blockIdx*blockDim+threadIdx+start
+    // IS the element index and its own algorithms use it as such
+    // (/root/reference scalix/algorithm/transform.cuh:58-59); with the persistent
+    // grid-stride launch used here the completed trips are added to keep that meaning.
     __device__ index_t global_thread_linear_id() const {
-        return index_t(blockIdx.x) * blockDim.x + threadIdx.x + start_linear_;
+        return index_t(blockIdx.x) * blockDim.x + threadIdx.x + start_linear_
+             + index_t(stride_count_) * (index_t(gridDim.x) * blockDim.x);
     }
     __device__ md_index_t<ProblemRank> global_thread_id() const {
         return md_index_t<>::create_from_linear(global_thread_linear_id(), global_range_);
