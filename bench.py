@@ -136,8 +136,10 @@ def run_reference(args):
         env = dict(os.environ)
         env["CUDA_VISIBLE_DEVICES"] = ",".join(str(i) for i in range(n))
         try:
-            out = subprocess.run([ref_bin, "bench_rld", str(ROWS), str(COLS * n), str(args.steps), str(args.warmup)],
+            out = subprocess.run([ref_bin, "bench", "rld_f32", str(COLS * n), str(args.steps), str(args.warmup)],
                                  capture_output=True, text=True, timeout=900, env=env)
+            if out.returncode != 0:
+                sys.stderr.write(f"reference UM build exited {out.returncode}: {out.stderr[-500:]}\n")
             for ln in out.stdout.splitlines():
                 if ln.startswith("{"):
                     r = json.loads(ln)
