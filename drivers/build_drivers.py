@@ -37,7 +37,11 @@ def build_one(src, out, extra=()):
 
 def main(force=False):
     os.makedirs(BIN, exist_ok=True)
-    jobs = [(os.path.join(HERE, "parity_driver.cu"), os.path.join(BIN, "parity_driver_ours"), ())]
+    # cereal is the reference's vendored third-party dependency (extern/cereal); only the
+    # optional serialize case of the driver needs it
+    cereal = "/root/reference/extern/cereal/include"
+    extra = ("-I", cereal) if os.path.isdir(cereal) else ()
+    jobs = [(os.path.join(HERE, "parity_driver.cu"), os.path.join(BIN, "parity_driver_ours"), extra)]
     if os.path.isdir(REF_EXAMPLES):
         for ex in EXAMPLES:
             jobs.append((os.path.join(REF_EXAMPLES, ex + ".cu"), os.path.join(BIN, "ex_" + ex), ("-I", REF_EXAMPLES)))

@@ -9,13 +9,21 @@
 //   parity_driver dump  <case> <n> <outfile>          run a parity case, dump raw result bytes
 //   parity_driver bench <case> <n> <steps> <warmup>   print {"ms_per_step": ..} (wall clock
 //                                                      around the blocking public API call)
-// cases: scan_i32 scan_i64 rld_f32 rld_u32max axpy_f32 axpy_f32_r3 gather_f32 fill_iota
+// cases: scan_i32 scan_i64 rld_f32 rld_u32max axpy_f32 axpy_f32_r3 gather_f32 fill_iota serialize
 #include <scalix/algorithm/inclusive_scan.cuh>
 #include <scalix/algorithm/reduce.cuh>
 #include <scalix/algorithm/reduce_last_dim.cuh>
 #include <scalix/fill.cuh>
 #include <scalix/iota.cuh>
 #include <scalix/scalix.cuh>
+
+#if defined(__has_include)
+#if __has_include(<cereal/archives/binary.hpp>)
+#include <cereal/archives/binary.hpp>
+#include <sstream>
+#define DRIVER_HAS_CEREAL 1
+#endif
+#endif
 
 #include <chrono>
 #include <cstdio>
@@ -216,6 +224,37 @@ int run_case(const std::string& what, const std::string& name, size_t n, const c
         }).get();
         return do_dump ? dump(r, path) : bench(step, steps, warmup);
     }
+#ifdef DRIVER_HAS_CEREAL
+    if (name == "serialize") {
+        // serialize_array / deserialize_array round trip through cereal's binary archives
+        // (scalix/array.cuh:907-950), then a kernel over the restored array
+        sclx::array<int, 3> a({3, 4, n / 12});
+        generate(a, [] __device__(size_t i) { return int(splitmix64(0x5E7, i)); });
+        std::stringstream ss;
+        {
+            cereal::BinaryOutputArchive oar(ss);
+            sclx::serialize_array(oar, a);
+        }
+        sclx::array<int, 3> b;
+        {
+            cereal::BinaryInputArchive iar(ss);
+            sclx::deserialize_array(iar, b);
+        }
+        if (b.shape() != a.shape()) return 5;
+        sclx::array<int, 3> r(a.shape());
+        auto step = [&] {
+            sclx::execute_kernel([&](sclx::kernel_handler& handler) {
+                handler.launch(
+                    sclx::md_range_t<3>{r.shape()},
+                    r,
+                    [=] __device__(const sclx::md_index_t<3>& idx, const auto&) { r[idx] = b[idx] + 1; }
+                );
+            }).get();
+        };
+        step();
+        return do_dump ? dump(r, path) : bench(step, steps, warmup);
+    }
+#endif
     std::fprintf(stderr, "unknown case %s\n", name.c_str());
     return 2;
 }

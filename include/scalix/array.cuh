@@ -34,6 +34,15 @@
 #include <tuple>
 #include <type_traits>
 #include <vector>
+// serialization helpers need cereal only where the consumer has it on the include path
+// (the reference vendors it as extern/cereal and includes it unconditionally, array.cuh:59-61)
+#if !defined(__CUDA_ARCH__) && defined(__has_include)
+#if __has_include(<cereal/cereal.hpp>)
+#include <cereal/archives/binary.hpp>
+#include <cereal/cereal.hpp>
+#define SCLX_B200_HAS_CEREAL 1
+#endif
+#endif
 
 namespace sclx {
 
@@ -745,6 +754,38 @@ get_device_split_info(const array<T, Rank>& arr) {
     }
     return splits;
 }
+
+#ifdef SCLX_B200_HAS_CEREAL
+// On-disk format of /root/reference scalix/array.cuh:907-950: Rank extents, then the payload
+// (one raw block for cereal::BinaryInputArchive, element by element for every other archive
+// — including BinaryOutputArchive, so a binary round trip is element-wise out, raw in; both
+// are the same bytes).  Host element access goes through the array's host mirror.
+template<class Archive, class T, uint Rank>
+__host__ void serialize_array(Archive& archive, const sclx::array<T, Rank>& array) {
+    for (uint d = 0; d < Rank; ++d) archive(array.shape()[d]);
+    if constexpr (std::is_same_v<Archive, cereal::BinaryInputArchive>) {
+        archive(cereal::binary_data(array.data().get(), array.elements() * sizeof(T)));
+    } else {
+        std::for_each(array.begin(), array.end(), [&](auto& element) { archive(element); });
+    }
+}
+
+template<class Archive, class T, uint Rank>
+__host__ void deserialize_array(Archive& archive, sclx::array<T, Rank>& array) {
+    sclx::shape_t<Rank> shape;
+    for (uint d = 0; d < Rank; ++d) archive(shape[d]);
+    array = sclx::array<T, Rank>{shape};
+    if constexpr (std::is_same_v<Archive, cereal::BinaryInputArchive>) {
+        // staged: a stream may read() straight into the destination, and a syscall cannot
+        // fault the host mirror in the way a user-space store does
+        std::vector<std::remove_const_t<T>> staged(array.elements());
+        archive(cereal::binary_data(staged.data(), staged.size() * sizeof(T)));
+        std::copy(staged.begin(), staged.end(), array.begin());
+    } else {
+        std::for_each(array.begin(), array.end(), [&](auto& element) { archive(element); });
+    }
+}
+#endif  // SCLX_B200_HAS_CEREAL
 
 __host__ inline bool is_same_device_split(
     const std::vector<std::tuple<int, size_t, size_t>>& lhs,

@@ -364,3 +364,86 @@ def test_inclusive_scan_host_chunks(sclx, oracle):
     out = np.zeros(n, np.int32)
     sclx.inclusive_scan_host(a, out, n, sclx.I32, sclx.PLUS)
     assert np.array_equal(out, np.cumsum(a.astype(np.uint32), dtype=np.uint32).view(np.int32))
+
+
+# ----------------------------------------------------------------------------- BASELINE.json full sizes
+def test_axpy_and_gather_config3_config4_full_size(sclx, oracle):
+    """configs[2] and configs[3] at their full sizes, bit-exact against the oracle on the same
+    index-keyed inputs: y = a*x + y over 2^30 f32 through the range dispatcher (8 partitions,
+    like 8 devices), then out[i] = src[index[i]] for 2^28 random u64 indices into that 2^30
+    array through the gather kernel (8 source partitions) and through the range launch."""
+    n, n_idx, chunk = 1 << 30, 1 << 28, 1 << 26
+    d_x, d_y = sclx.DeviceBuffer(n * 4), sclx.DeviceBuffer(n * 4)
+    for c in range(0, n, chunk):  # generate + upload in 256 MiB chunks (bounded host memory)
+        x, y = oracle.symmetric_f32(chunk, 1, first=c), oracle.symmetric_f32(chunk, 2, first=c)
+        sclx.check(sclx.lib.sclx_b200_memcpy_h2d(d_x.ptr + c * 4, x.ctypes.data, x.nbytes, None))
+        sclx.check(sclx.lib.sclx_b200_memcpy_h2d(d_y.ptr + c * 4, y.ctypes.data, y.nbytes, None))
+        sclx.synchronize()
+    sclx.axpy_f32(1.5, d_x.ptr, d_y.ptr, n, 8)
+    for c in range(0, n, chunk):
+        x, y = oracle.symmetric_f32(chunk, 1, first=c), oracle.symmetric_f32(chunk, 2, first=c)
+        got = d_y.to_numpy(np.float32, count=chunk, offset_bytes=c * 4)
+        assert np.array_equal(got.view(np.uint32), oracle.axpy_f32(1.5, x, y).view(np.uint32)), f"axpy chunk at {c}"
+    del d_y
+
+    # gather: the source is x (regenerated on the host once: 4 GiB)
+    src = np.empty(n, np.float32)
+    for c in range(0, n, chunk):
+        src[c:c + chunk] = oracle.symmetric_f32(chunk, 1, first=c)
+    d_idx, d_out = sclx.DeviceBuffer(n_idx * 8), sclx.DeviceBuffer(n_idx * 4)
+    for c in range(0, n_idx, chunk):
+        idx = oracle.index_u64(chunk, 0x6A7, n, first=c)
+        sclx.check(sclx.lib.sclx_b200_memcpy_h2d(d_idx.ptr + c * 8, idx.ctypes.data, idx.nbytes, None))
+        sclx.synchronize()
+    per = n // 8
+    parts = [d_x.ptr + p * per * 4 for p in range(8)]
+    for how in ("kernel", "launch"):
+        sclx.fill(d_out, n_idx, 0, np.uint32)
+        if how == "kernel":
+            sclx.gather(d_idx.ptr, n_idx, 8, parts, per, 4, d_out.ptr)
+        else:
+            sclx.gather_launch_f32(d_idx.ptr, n_idx, d_x.ptr, d_out.ptr, 8)
+        for c in range(0, n_idx, chunk):
+            idx = oracle.index_u64(chunk, 0x6A7, n, first=c)
+            got = d_out.to_numpy(np.float32, count=chunk, offset_bytes=c * 4)
+            assert np.array_equal(got.view(np.uint32), oracle.gather(src, idx).view(np.uint32)), f"{how} chunk at {c}"
+
+
+def test_scan_config5_full_size_closed_form(sclx):
+    """configs[4]: inclusive_scan over 2^32 int64, partitioned like 8 devices (pass A totals +
+    carry-seeded single-pass scans), on one GPU (32 GiB in + 32 GiB out).  Input iota(0), so
+    out[i] = i(i+1)/2 mod 2^64: checked at the last element, in windows around every partition
+    boundary, and through a checksum of the whole output (our reduce kernel, mod 2^64)
+    = n(n+1)(n+2)/6.  The reference itself cannot run this size on one device (32-bit thread
+    arithmetic, scalix/kernel_info.cuh:86-101)."""
+    n, ndev, item = 1 << 32, 8, 8
+    d_in, d_out = sclx.DeviceBuffer(n * item), sclx.DeviceBuffer(n * item)
+    sclx.iota(d_in, n, sclx.I64, 0)
+    parts = sclx.partition(n, ndev)
+    totals = sclx.DeviceBuffer(8 * ndev)
+    for d, (s, ln) in enumerate(parts):
+        sclx.reduce(d_in, ln, sclx.I64, sclx.PLUS, 0, totals.ptr + d * item, in_offset=s * item)
+    for d, (s, ln) in enumerate(parts):
+        sclx.inclusive_scan(d_in, d_out, ln, sclx.I64, sclx.PLUS, lower_totals=totals.ptr, n_lower=d,
+                            in_offset=s * item, out_offset=s * item)
+    m64 = (1 << 64) - 1
+
+    def closed(i):
+        return (i * (i + 1) // 2) & m64
+
+    win = 4096
+    starts = {0, n - win}
+    for s, ln in parts[1:]:
+        starts.update({s - win, s, s + 12345})
+    for s in sorted(starts):
+        got = d_out.to_numpy(np.uint64, count=win, offset_bytes=s * item)
+        want = np.array([closed(i) for i in range(s, s + win)], dtype=np.uint64)
+        assert np.array_equal(got, want), f"window at {s}"
+    chk = sclx.DeviceBuffer(16)
+    sclx.reduce(d_out, n, sclx.U64, sclx.PLUS, 0, chk.ptr)
+    assert int(chk.to_numpy(np.uint64)[0]) == (n * (n + 1) * (n + 2) // 6) & m64
+    # the single-partition (pure single-pass) scan of the same input must give the same checksum
+    sclx.inclusive_scan(d_in, d_out, n, sclx.I64, sclx.PLUS)
+    sclx.reduce(d_out, n, sclx.U64, sclx.PLUS, 0, chk.ptr)
+    assert int(chk.to_numpy(np.uint64)[0]) == (n * (n + 1) * (n + 2) // 6) & m64
+    assert int(d_out.to_numpy(np.uint64, count=1, offset_bytes=(n - 1) * item)[0]) == closed(n - 1)

@@ -29,15 +29,24 @@ CASES = {  # name -> (n, dtype, float tolerance or None)
     "axpy_f32_r3": (1 << 20, np.float32, None),
     "gather_f32": (300_007, np.float32, None),
     "fill_iota": (1 << 16, np.int32, None),
+    "serialize": (12 * 40_001, np.int32, None),
 }
 
 
-def run_dump(binary, case, n, path, emulate=None):
+def visible_gpus():
+    try:
+        out = subprocess.run(["nvidia-smi", "-L"], capture_output=True, text=True, timeout=30).stdout
+        return sum(1 for ln in out.splitlines() if ln.startswith("GPU "))
+    except Exception:
+        return 0
+
+
+def run_dump(binary, case, n, path, emulate=None, real_devices=1):
     env = dict(os.environ)
     env.pop("SCLX_B200_EMULATE_DEVICES", None)
     if emulate:
         env["SCLX_B200_EMULATE_DEVICES"] = str(emulate)
-    env["CUDA_VISIBLE_DEVICES"] = env.get("CUDA_VISIBLE_DEVICES", "0").split(",")[0]
+    env["CUDA_VISIBLE_DEVICES"] = ",".join(str(i) for i in range(real_devices))
     p = subprocess.run([binary, "dump", case, str(n), path], capture_output=True, text=True, timeout=600, env=env)
     assert p.returncode == 0, f"{os.path.basename(binary)} {case}: rc={p.returncode}\n{p.stdout}\n{p.stderr}"
 
@@ -59,6 +68,9 @@ def oracle_expected(oracle, case, n):
     if case == "rld_u32max":
         col = np.array([oracle.lib.oracle_splitmix64(j, 7) % 1000003 for j in range(n)], dtype=np.uint64)
         return (int(col.max()) + np.tile(np.arange(3, dtype=np.uint32), 9)).astype(np.uint32)
+    if case == "serialize":
+        v = np.array([oracle.lib.oracle_splitmix64(0x5E7, i) & 0xFFFFFFFF for i in range(n)], dtype=np.uint64)
+        return (v + np.uint64(1)).astype(np.uint32).view(np.int32)
     if case == "fill_iota":
         return (41 + 1 + np.arange(n, dtype=np.int64)).astype(np.int32)
     return None
@@ -97,6 +109,27 @@ def test_driver_case_matches_reference_and_oracle(binaries, oracle, tmp_path, ca
         compare(got, np.fromfile(theirs, dtype=dtype), tol, f"{case}: ours (emulate={emulate}) vs reference UM build")
     else:
         assert want is not None or emulate is not None, f"{case}: nothing to compare with"
+
+
+@pytest.mark.parametrize("case", sorted(CASES))
+def test_driver_case_on_real_multi_gpu(binaries, oracle, tmp_path, case):
+    """every visible GPU as one partition (VMM pages on their owners, peer-mapped VA, NVLink
+    loads/stores for the cross-partition accesses) — skipped on a single-GPU box"""
+    ngpu = visible_gpus()
+    if ngpu < 2:
+        pytest.skip("needs >= 2 GPUs")
+    ours, ref = binaries
+    n, dtype, tol = CASES[case]
+    mine = str(tmp_path / "ours.bin")
+    run_dump(ours, case, n, mine, real_devices=ngpu)
+    got = np.fromfile(mine, dtype=dtype)
+    want = oracle_expected(oracle, case, n)
+    if want is not None:
+        compare(got, want, tol, f"{case}: ours on {ngpu} GPUs vs CPU oracle")
+    if ref is not None:
+        theirs = str(tmp_path / "ref.bin")
+        run_dump(ref, case, n, theirs, real_devices=ngpu)
+        compare(got, np.fromfile(theirs, dtype=dtype), tol, f"{case}: ours vs reference UM build, {ngpu} GPUs")
 
 
 def run_example(name, emulate=None, timeout=900):
