@@ -9,7 +9,7 @@
 //   parity_driver dump  <case> <n> <outfile>          run a parity case, dump raw result bytes
 //   parity_driver bench <case> <n> <steps> <warmup>   print {"ms_per_step": ..} (wall clock
 //                                                      around the blocking public API call)
-// cases: scan_i32 scan_i64 rld_f32 rld_u32max axpy_f32 axpy_f32_r3 gather_f32 fill_iota serialize
+// cases: scan_i32 scan_i64 rld_f32 rld_u32max axpy_f32 axpy_f32_r3 gather_f32 fill_iota serialize gather_x_f32 gather_x_f64 gather_x_skew
 #include <scalix/algorithm/inclusive_scan.cuh>
 #include <scalix/algorithm/reduce.cuh>
 #include <scalix/algorithm/reduce_last_dim.cuh>
@@ -22,6 +22,13 @@
 #include <cereal/archives/binary.hpp>
 #include <sstream>
 #define DRIVER_HAS_CEREAL 1
+#endif
+#endif
+
+#if defined(__has_include)
+#if __has_include(<scalix/algorithm/gather.cuh>)
+#include <scalix/algorithm/gather.cuh>  // extension of this repository; the reference build uses the lambda idiom
+#define DRIVER_HAS_GATHER 1
 #endif
 #endif
 
@@ -96,6 +103,35 @@ int bench(Step&& step, int steps, int warmup) {
 // ---- cases --------------------------------------------------------------------------------
 // every case: build inputs with the public API, run the public API call under test; `out`
 // receives the array to dump; `step` re-runs only the call under test (for bench)
+
+template<class T>
+int gather_x(bool do_dump, size_t n, const char* path, int steps, int warmup, bool skew = false) {
+    sclx::array<T, 1> src({4 * n}), out({n});
+    sclx::array<size_t, 1> index({n});
+    // skew: every index falls into the first eighth of the source (one owner's queue overflows)
+    const size_t m = skew ? n / 2 : 4 * n;
+    generate(src, [] __device__(size_t i) { return T(uniform01(0xABC, i)) + T(i >> 20); });
+    generate(index, [=] __device__(size_t i) { return size_t(splitmix64(0x6A7, i) % m); });
+    auto step = [&] {
+#ifdef DRIVER_HAS_GATHER
+        auto mode         = sclx::algorithm::gather_mode::automatic;
+        const char* force = std::getenv("SCLX_GATHER_MODE");
+        if (force && !std::strcmp(force, "exchange")) mode = sclx::algorithm::gather_mode::exchange;
+        if (force && !std::strcmp(force, "direct")) mode = sclx::algorithm::gather_mode::direct;
+        sclx::algorithm::gather(src, index, out, mode);
+#else
+        sclx::execute_kernel([&](sclx::kernel_handler& handler) {
+            handler.launch(
+                sclx::md_range_t<1>{out.shape()},
+                out,
+                [=] __device__(const sclx::md_index_t<1>& idx, const auto&) { out[idx] = src[index[idx]]; }
+            );
+        }).get();
+#endif
+    };
+    step();
+    return do_dump ? dump(out, path) : bench(step, steps, warmup);
+}
 
 int run_case(const std::string& what, const std::string& name, size_t n, const char* path, int steps, int warmup) {
     const bool do_dump = what == "dump";
@@ -202,6 +238,13 @@ int run_case(const std::string& what, const std::string& name, size_t n, const c
         };
         step();
         return do_dump ? dump(out, path) : bench(step, steps, warmup);
+    }
+    if (name == "gather_x_skew") return gather_x<float>(do_dump, n, path, steps, warmup, true);
+    if (name == "gather_x_f32" || name == "gather_x_f64") {
+        // configs[3] through the framework-owned gather (exchange form across partitions); the
+        // reference build runs the same gather as the user-lambda idiom it documents
+        return name == "gather_x_f32" ? gather_x<float>(do_dump, n, path, steps, warmup)
+                                      : gather_x<double>(do_dump, n, path, steps, warmup);
     }
     if (name == "fill_iota") {
         // fill a rank-3 array, iota a rank-1 array, add them element-wise through a lambda

@@ -1,0 +1,249 @@
+// scalix-b200: algorithm::gather — out[i] = src[index[i]] over partitioned arrays.
+//
+// EXTENSION: the reference has no gather entry point; its users write the gather as a lambda
+// over the range launcher (/root/reference examples/distributed_indexing.cu:146-154,
+// examples/scaling_performance.cu:59-78) and Unified Memory faults the remote pages in.  That
+// idiom keeps working here unchanged (cross-partition reads are NVLink peer loads on the
+// array's peer-mapped range), but one peer load per index is capped by NVLink's request rate
+// (detail/b200/gather_exchange.cuh).  This entry point is the framework-owned form of the same
+// operation: `index` holds linear (storage-order) indices into `src`; `out` and `index` have
+// the same length; result bits are those of the lambda form.
+//
+//   1 source partition, or shapes the exchange does not cover -> direct kernel (peer loads)
+//   otherwise                                                  -> exchange form (K1/K2/K3)
+//
+// Blocking, like the reference's algorithms.
+#pragma once
+#include "../detail/b200/gather_exchange.cuh"
+#include "../detail/b200/host_launch.cuh"
+#include "../execute_kernel.cuh"
+
+#include <cstdlib>
+#include <type_traits>
+#include <vector>
+
+namespace sclx::algorithm {
+
+enum class gather_mode { automatic, direct, exchange };
+
+namespace detail {
+
+template<size_t Bytes>
+struct gather_carrier;
+template<>
+struct gather_carrier<4> {
+    using type = unsigned;
+};
+template<>
+struct gather_carrier<8> {
+    using type = unsigned long long;
+};
+
+inline size_t gx_align(size_t v) { return (v + 255) & ~size_t(255); }
+
+inline unsigned gx_capacity(size_t n_requester, int nowners) {
+    // 1.25 x the uniform share + one tile, never more than the requester's whole partition
+    const size_t share = (n_requester + nowners - 1) / nowners;
+    size_t cap         = share + share / 4 + b200::kGxTile;
+    if (cap > n_requester) cap = n_requester;
+    cap = (cap + 31) & ~size_t(31);
+    return unsigned(cap);
+}
+
+}  // namespace detail
+
+template<class T, uint Rank, class I>
+__host__ void gather(
+    const array<const T, Rank>& src,
+    const array<I, 1>& index,
+    array<T, 1>& out,
+    gather_mode mode = gather_mode::automatic
+) {
+    static_assert(std::is_trivially_copyable_v<T>, "gather: element type must be trivially copyable");
+    static_assert(std::is_integral_v<std::remove_const_t<I>>, "gather: index type must be integral");
+    if (index.elements() != out.elements())
+        throw_exception<std::invalid_argument>(
+            "index and result arrays must have the same length", "sclx::algorithm::"
+        );
+    const size_t n = out.elements();
+    if (n == 0) return;
+    const int caller_device = cuda::traits::current_device();
+    const auto out_info     = get_device_split_info(out);
+    const auto src_info     = get_device_split_info(src);
+    const int nreq          = int(out_info.size());
+    const int nown          = int(src_info.size());
+    const size_t src_last   = src.shape()[Rank - 1];
+    const size_t src_lead   = src_last ? src.elements() / src_last : 0;
+    using index_t_          = std::remove_const_t<I>;
+    const index_t_* idx_ptr = index.data().get();
+
+    bool exchange_ok = (sizeof(T) == 4 || sizeof(T) == 8) && nown > 1 && nown <= b200::kGxMaxParts
+                       && nreq <= b200::kGxMaxParts && n < (size_t(1) << 32) * size_t(nreq);
+    // owners must be uniform blocks of `per` elements starting at p*per (true for every
+    // array partitioned by set_primary_devices; not for arbitrary slices), distinct devices
+    size_t per = 0;
+    if (exchange_ok) {
+        per = std::get<2>(src_info[0]) * src_lead;
+        for (int p = 0; p < nown && exchange_ok; ++p) {
+            if (std::get<1>(src_info[p]) * src_lead != size_t(p) * per) exchange_ok = false;
+            for (int o = 0; o < p; ++o)
+                if (std::get<0>(src_info[o]) == std::get<0>(src_info[p])) exchange_ok = false;
+        }
+        for (int r = 0; r < nreq && exchange_ok; ++r)
+            for (int o = 0; o < r; ++o)
+                if (std::get<0>(out_info[o]) == std::get<0>(out_info[r])) exchange_ok = false;
+        if (per == 0 || per > (size_t(1) << 32)) exchange_ok = false;
+    }
+    if (mode == gather_mode::exchange && !exchange_ok)
+        throw_exception<std::invalid_argument>(
+            "exchange gather needs 4- or 8-byte elements and a source partitioned in uniform blocks over "
+            "2..16 distinct devices",
+            "sclx::algorithm::"
+        );
+    const bool use_exchange
+        = exchange_ok && (mode == gather_mode::exchange || (mode == gather_mode::automatic && n >= (size_t(1) << 18)));
+
+    if constexpr (sizeof(T) != 4 && sizeof(T) != 8) {
+        // direct kernel on raw element type
+        b200::for_each_partition(out, out_info, [&](const b200::partition_t& p) {
+            if (p.elements == 0) return;
+            const size_t work = (p.elements + 255) / 256;
+            b200::gather_direct_kernel<T, index_t_, 256, 4>
+                <<<b200::persistent_grid(work, 8, b200::sm_count_of(p.device)), 256, 0, p.stream>>>(
+                    idx_ptr + p.offset, p.elements, src.data().get(), out.data().get() + p.offset
+                );
+        });
+    } else {
+        using U           = typename detail::gather_carrier<sizeof(T)>::type;
+        const U* src_base = reinterpret_cast<const U*>(src.data().get());
+        U* out_base       = reinterpret_cast<U*>(out.data().get());
+        if (!use_exchange) {
+            b200::for_each_partition(out, out_info, [&](const b200::partition_t& p) {
+                if (p.elements == 0) return;
+                const size_t work = (p.elements + 255) / 256;
+                b200::gather_direct_kernel<U, index_t_, 256, 8>
+                    <<<b200::persistent_grid(work, 8, b200::sm_count_of(p.device)), 256, 0, p.stream>>>(
+                        idx_ptr + p.offset, p.elements, src_base, out_base + p.offset
+                    );
+            });
+        } else {
+            // ---- workspace layout, per logical device ------------------------------------
+            std::vector<size_t> n_r(nreq), tiles_r(nreq);
+            std::vector<std::vector<unsigned>> cap(nreq, std::vector<unsigned>(nown));
+            for (int r = 0; r < nreq; ++r) {
+                n_r[r]     = std::get<2>(out_info[r]);
+                tiles_r[r] = (n_r[r] + b200::kGxTile - 1) / b200::kGxTile;
+                for (int q = 0; q < nown; ++q) cap[r][q] = n_r[r] ? detail::gx_capacity(n_r[r], nown) : 0;
+            }
+            struct dev_layout {
+                int device;
+                size_t bytes = 0;
+                char* base   = nullptr;
+            };
+            std::vector<dev_layout> devs;
+            auto dev_slot = [&](int device) -> dev_layout& {
+                for (auto& d : devs)
+                    if (d.device == device) return d;
+                devs.push_back(dev_layout{device});
+                return devs.back();
+            };
+            auto reserve = [&](int device, size_t bytes) {
+                dev_layout& d    = dev_slot(device);
+                const size_t off = d.bytes;
+                d.bytes += detail::gx_align(bytes);
+                return off;
+            };
+            // offsets (filled in below once the bases are known)
+            std::vector<std::vector<size_t>> queue_off(nreq, std::vector<size_t>(nown)),
+                resp_off(nreq, std::vector<size_t>(nown));
+            std::vector<size_t> counters_off(nreq), pos_off(nreq), tbase_off(nreq), tcnt_off(nreq);
+            for (int r = 0; r < nreq; ++r) {
+                const int rdev  = std::get<0>(out_info[r]);
+                counters_off[r] = reserve(rdev, sizeof(unsigned) * b200::kGxMaxParts);
+                pos_off[r]      = reserve(rdev, tiles_r[r] * b200::kGxTile * sizeof(unsigned short));
+                tbase_off[r]    = reserve(rdev, tiles_r[r] * nown * sizeof(unsigned));
+                tcnt_off[r]     = reserve(rdev, tiles_r[r] * nown * sizeof(unsigned short));
+                for (int q = 0; q < nown; ++q) {
+                    resp_off[r][q]  = reserve(rdev, size_t(cap[r][q]) * sizeof(U));
+                    queue_off[r][q] = reserve(std::get<0>(src_info[q]), size_t(cap[r][q]) * sizeof(unsigned));
+                }
+            }
+            for (auto& d : devs) {
+                void* ptr = nullptr;
+                cuda::detail::check_rt(sclx_b200_rt_exchange_workspace(d.device, d.bytes, &ptr));
+                d.base = static_cast<char*>(ptr);
+            }
+            auto at = [&](int device, size_t off) { return dev_slot(device).base + off; };
+
+            const b200::gx_div_t div = b200::gx_make_div(per);
+            std::vector<b200::gx_requester_t<U>> rq(nreq);
+            for (int r = 0; r < nreq; ++r) {
+                const int rdev = std::get<0>(out_info[r]);
+                auto& x        = rq[r];
+                x.out          = out_base + std::get<1>(out_info[r]);
+                x.src_base     = src_base;
+                x.n            = n_r[r];
+                x.nowners      = nown;
+                x.div          = div;
+                x.counters     = reinterpret_cast<unsigned*>(at(rdev, counters_off[r]));
+                x.pos          = reinterpret_cast<unsigned short*>(at(rdev, pos_off[r]));
+                x.tile_base    = reinterpret_cast<unsigned*>(at(rdev, tbase_off[r]));
+                x.tile_cnt     = reinterpret_cast<unsigned short*>(at(rdev, tcnt_off[r]));
+                for (int q = 0; q < nown; ++q) {
+                    x.queue[q] = reinterpret_cast<unsigned*>(at(std::get<0>(src_info[q]), queue_off[r][q]));
+                    x.cap[q]   = cap[r][q];
+                    x.resp[q]  = reinterpret_cast<U*>(at(rdev, resp_off[r][q]));
+                }
+            }
+            std::vector<b200::gx_owner_t<U>> ow(nown);
+            for (int q = 0; q < nown; ++q) {
+                auto& y     = ow[q];
+                y.src_local = src_base + size_t(q) * per;
+                y.nreq      = nreq;
+                for (int r = 0; r < nreq; ++r) {
+                    y.queue[r]   = rq[r].queue[q];
+                    y.counter[r] = rq[r].counters + q;
+                    y.cap[r]     = cap[r][q];
+                    y.resp[r]    = rq[r].resp[q];
+                }
+            }
+            // ---- three launch groups --------------------------------------------------------
+            b200::for_each_partition(out, out_info, [&](const b200::partition_t& p) {
+                const auto& x = rq[p.ordinal];
+                if (x.n == 0) return;
+                cuda::cuda_exception::raise_if_not_success(
+                    cudaMemsetAsync(x.counters, 0, sizeof(unsigned) * b200::kGxMaxParts, p.stream),
+                    std::experimental::source_location::current(),
+                    "sclx::algorithm::"
+                );
+                const unsigned grid
+                    = b200::persistent_grid(tiles_r[p.ordinal], 3, b200::sm_count_of(p.device));
+                b200::gx_partition_kernel<U, index_t_>
+                    <<<grid, b200::kGxThreads, 0, p.stream>>>(x, idx_ptr + p.offset);
+            });
+            b200::for_each_partition(src, src_info, [&](const b200::partition_t& p) {
+                b200::gx_serve_kernel<U, 256, 4>
+                    <<<unsigned(b200::sm_count_of(p.device)) * 8u, 256, 0, p.stream>>>(ow[p.ordinal]);
+            });
+            b200::for_each_partition(out, out_info, [&](const b200::partition_t& p) {
+                const auto& x = rq[p.ordinal];
+                if (x.n == 0) return;
+                const unsigned grid
+                    = b200::persistent_grid(tiles_r[p.ordinal], 4, b200::sm_count_of(p.device));
+                b200::gx_place_kernel<U><<<grid, b200::kGxThreads, 0, p.stream>>>(x);
+            });
+        }
+    }
+    std::vector<int> devices = b200::devices_of(out_info);
+    for (int d : b200::devices_of(src_info)) devices.push_back(d);
+    b200::sync_devices(devices);
+    cuda::set_device(caller_device);
+}
+
+template<class T, uint Rank, class I>
+__host__ void
+gather(const array<T, Rank>& src, const array<I, 1>& index, array<T, 1>& out, gather_mode mode = gather_mode::automatic) {
+    gather(static_cast<const array<const T, Rank>&>(src), index, out, mode);
+}
+
+}  // namespace sclx::algorithm

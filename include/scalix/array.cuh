@@ -36,11 +36,13 @@
 #include <vector>
 // serialization helpers need cereal only where the consumer has it on the include path
 // (the reference vendors it as extern/cereal and includes it unconditionally, array.cuh:59-61)
-#if !defined(__CUDA_ARCH__) && defined(__has_include)
+#if defined(__has_include)
 #if __has_include(<cereal/cereal.hpp>)
+#define SCLX_B200_HAS_CEREAL 1
+#ifndef __CUDA_ARCH__
 #include <cereal/archives/binary.hpp>
 #include <cereal/cereal.hpp>
-#define SCLX_B200_HAS_CEREAL 1
+#endif
 #endif
 #endif
 
@@ -762,16 +764,19 @@ get_device_split_info(const array<T, Rank>& arr) {
 // are the same bytes).  Host element access goes through the array's host mirror.
 template<class Archive, class T, uint Rank>
 __host__ void serialize_array(Archive& archive, const sclx::array<T, Rank>& array) {
+#ifndef __CUDA_ARCH__
     for (uint d = 0; d < Rank; ++d) archive(array.shape()[d]);
     if constexpr (std::is_same_v<Archive, cereal::BinaryInputArchive>) {
         archive(cereal::binary_data(array.data().get(), array.elements() * sizeof(T)));
     } else {
         std::for_each(array.begin(), array.end(), [&](auto& element) { archive(element); });
     }
+#endif
 }
 
 template<class Archive, class T, uint Rank>
 __host__ void deserialize_array(Archive& archive, sclx::array<T, Rank>& array) {
+#ifndef __CUDA_ARCH__
     sclx::shape_t<Rank> shape;
     for (uint d = 0; d < Rank; ++d) archive(shape[d]);
     array = sclx::array<T, Rank>{shape};
@@ -784,6 +789,7 @@ __host__ void deserialize_array(Archive& archive, sclx::array<T, Rank>& array) {
     } else {
         std::for_each(array.begin(), array.end(), [&](auto& element) { archive(element); });
     }
+#endif
 }
 #endif  // SCLX_B200_HAS_CEREAL
 

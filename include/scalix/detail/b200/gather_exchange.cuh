@@ -1,0 +1,264 @@
+// scalix-b200: exchange form of the cross-partition gather  out[i] = src[index[i]].
+//
+// Why it exists (experiments/p2p_probe.cu on 2 x B200, profiles/r01_p2p_probe.txt): NVLink 5
+// P2P serves about 6.5 G REQUESTS/s per GPU whatever the request carries — a random 4-byte
+// peer load, a 16-byte one, a posted 4-byte store and a fully coalesced 128-byte line all cost
+// one request.  A gather that issues one peer load per index (what a user lambda over the
+// range launcher does, and all an opaque lambda can do) is therefore capped at ~26 GB/s of
+// payload, 3 % of the link, while local HBM serves 40 G random 4-byte reads/s.  The exchange
+// form moves the same data in 128-byte requests only:
+//
+//   K1  partition (requester r, one CTA per 4096-index tile): classify every index by owning
+//       partition q, bucket the tile in shared memory, reserve a run in the (r -> q) request
+//       queue with ONE atomic per bucket and write the 32-bit in-partition offsets to the queue
+//       IN OWNER q's MEMORY with coalesced posted stores; keep the 16-bit in-tile positions
+//       locally, in the same order.
+//   K2  serve (owner q): stream its queues, gather from its LOCAL partition (HBM random reads)
+//       and write the values, in queue order, to the response buffer IN REQUESTER r's MEMORY
+//       (coalesced posted stores).
+//   K3  place (requester r): stream responses + positions, scatter inside the tile's 16 KiB
+//       window of `out`.
+//
+// The three kernels are three launch groups (ordered across devices by stream events, no host
+// round trip).  Queues have bounded capacity (1.25 x the uniform share + one tile); an index
+// that finds its queue full is served by a direct peer load in K1, so skewed index sets stay
+// correct and merely lose the speed-up.  Pure data movement: results are bit-identical to the
+// direct gather whatever the order the queues were filled in.
+#pragma once
+
+#include "primitives.cuh"
+
+#include <cstdint>
+
+namespace sclx::b200 {
+
+constexpr int kGxMaxParts  = 16;
+constexpr int kGxThreads   = 512;
+constexpr int kGxPerThread = 8;
+constexpr int kGxTile      = kGxThreads * kGxPerThread;  // 4096 indices per tile
+
+// e / per and e % per with one 64x64 high multiply (per is the same for every partition but
+// the last: ceil(last/ndev) * leading elements)
+struct gx_div_t {
+    unsigned long long per, magic;
+};
+__host__ inline gx_div_t gx_make_div(unsigned long long per) {
+    return gx_div_t{per, per ? ~0ull / per : 0ull};
+}
+__host__ __device__ __forceinline__ void
+gx_owner(unsigned long long e, const gx_div_t& d, unsigned& q, unsigned& off) {
+#ifdef __CUDA_ARCH__
+    unsigned long long qq = __umul64hi(e, d.magic);
+#else
+    unsigned long long qq = (unsigned long long)(((unsigned __int128)e * d.magic) >> 64);
+#endif
+    unsigned long long r = e - qq * d.per;
+    if (r >= d.per) {
+        ++qq;
+        r -= d.per;
+    }
+    q   = unsigned(qq);
+    off = unsigned(r);
+}
+
+template<class U>  // U: unsigned carrier of the element width
+struct gx_requester_t {
+    U* out;             // this partition of `out`
+    const U* src_base;  // element 0 of the whole source (direct path when a queue is full)
+    size_t n;           // indices in this partition
+    int nowners;
+    gx_div_t div;
+    unsigned* queue[kGxMaxParts];  // (this requester -> q) offsets, in owner q's memory
+    unsigned cap[kGxMaxParts];     // capacity of that queue / response buffer
+    U* resp[kGxMaxParts];          // responses from owner q, local
+    unsigned* counters;            // [nowners] entries reserved so far, local
+    unsigned short* pos;           // [tiles * kGxTile] in-tile positions of queued entries
+    unsigned* tile_base;           // [tiles][nowners] first queue slot of the tile's run
+    unsigned short* tile_cnt;      // [tiles][nowners] length of that run
+};
+
+template<class U>
+struct gx_owner_t {
+    const U* src_local;  // first element of this partition of the source
+    int nreq;
+    const unsigned* queue[kGxMaxParts];    // (r -> this owner) offsets, local
+    const unsigned* counter[kGxMaxParts];  // &counters_r[this owner], in requester r's memory
+    unsigned cap[kGxMaxParts];
+    U* resp[kGxMaxParts];  // response buffer for this owner, in requester r's memory
+};
+
+// ---- K1 -----------------------------------------------------------------------------------
+template<class U, class I>
+__global__ void __launch_bounds__(kGxThreads)
+    gx_partition_kernel(gx_requester_t<U> rq, const I* __restrict__ index) {
+    __shared__ unsigned s_off[kGxTile];
+    __shared__ unsigned short s_pos[kGxTile];
+    __shared__ unsigned s_cnt[kGxMaxParts], s_start[kGxMaxParts + 1], s_gbase[kGxMaxParts],
+        s_take[kGxMaxParts];
+    const int tid        = threadIdx.x;
+    const unsigned lane  = tid & 31;
+    const unsigned below = (1u << lane) - 1u;
+    const int nown       = rq.nowners;
+    const size_t tiles   = (rq.n + kGxTile - 1) / kGxTile;
+
+    for (size_t t = blockIdx.x; t < tiles; t += gridDim.x) {
+        if (tid < nown) s_cnt[tid] = 0;
+        __syncthreads();
+        const size_t tbase = t * kGxTile;
+        unsigned long long e[kGxPerThread];
+        unsigned q[kGxPerThread], off[kGxPerThread], rank[kGxPerThread];
+#pragma unroll
+        for (int k = 0; k < kGxPerThread; ++k) {
+            const size_t j = tbase + size_t(k) * kGxThreads + tid;
+            e[k]           = j < rq.n ? (unsigned long long)__ldg(index + j) : ~0ull;
+        }
+#pragma unroll
+        for (int k = 0; k < kGxPerThread; ++k) {
+            const bool valid = tbase + size_t(k) * kGxThreads + tid < rq.n;
+            q[k] = 0xffffffffu, off[k] = 0;
+            if (valid) {
+                gx_owner(e[k], rq.div, q[k], off[k]);
+                if (q[k] >= unsigned(nown)) q[k] = unsigned(nown) - 1;  // out of range: UB upstream too
+            }
+            // one shared-memory atomic per (warp, owner)
+            const unsigned peers = __match_any_sync(0xffffffffu, q[k]);
+            const int leader     = __ffs(peers) - 1;
+            unsigned first       = 0;
+            if (int(lane) == leader && valid) first = atomicAdd(&s_cnt[q[k]], unsigned(__popc(peers)));
+            first   = __shfl_sync(0xffffffffu, first, leader);
+            rank[k] = first + unsigned(__popc(peers & below));
+        }
+        __syncthreads();
+        if (tid < nown) {
+            const unsigned c    = s_cnt[tid];
+            const unsigned g    = c ? atomicAdd(&rq.counters[tid], c) : 0u;
+            const unsigned room = g < rq.cap[tid] ? rq.cap[tid] - g : 0u;
+            const unsigned take = c < room ? c : room;
+            s_gbase[tid]        = g;
+            s_take[tid]         = take;
+            rq.tile_base[t * nown + tid] = g;
+            rq.tile_cnt[t * nown + tid]  = (unsigned short)take;
+        }
+        __syncthreads();
+        if (tid == 0) {
+            unsigned acc = 0;
+            for (int o = 0; o < nown; ++o) {
+                s_start[o] = acc;
+                acc += s_take[o];
+            }
+            s_start[nown] = acc;
+        }
+        __syncthreads();
+#pragma unroll
+        for (int k = 0; k < kGxPerThread; ++k) {
+            const size_t j = tbase + size_t(k) * kGxThreads + tid;
+            if (j < rq.n) {
+                if (rank[k] < s_take[q[k]]) {
+                    const unsigned slot = s_start[q[k]] + rank[k];
+                    s_off[slot]         = off[k];
+                    s_pos[slot]         = (unsigned short)(k * kGxThreads + tid);
+                } else {
+                    rq.out[j] = rq.src_base[e[k]];  // queue full: direct (peer) load
+                }
+            }
+        }
+        __syncthreads();
+        const unsigned total = s_start[nown];
+        for (unsigned i = tid; i < total; i += kGxThreads) {
+            int o = 0;
+            while (i >= s_start[o + 1]) ++o;
+            rq.queue[o][s_gbase[o] + (i - s_start[o])] = s_off[i];
+            rq.pos[tbase + i]                          = s_pos[i];
+        }
+        __syncthreads();
+    }
+}
+
+// ---- K2 -----------------------------------------------------------------------------------
+template<class U, int THREADS, int UNROLL>
+__global__ void __launch_bounds__(THREADS) gx_serve_kernel(gx_owner_t<U> ow) {
+    const size_t gtid    = size_t(blockIdx.x) * THREADS + threadIdx.x;
+    const size_t gstride = size_t(gridDim.x) * THREADS;
+    for (int r = 0; r < ow.nreq; ++r) {
+        unsigned cnt = __ldcg(ow.counter[r]);
+        if (cnt > ow.cap[r]) cnt = ow.cap[r];
+        const unsigned* __restrict__ queue = ow.queue[r];
+        U* __restrict__ resp               = ow.resp[r];
+        size_t i                           = gtid;
+        for (; i + (UNROLL - 1) * gstride < cnt; i += UNROLL * gstride) {
+            unsigned o[UNROLL];
+#pragma unroll
+            for (int u = 0; u < UNROLL; ++u) o[u] = __ldcs(queue + i + u * gstride);
+            U v[UNROLL];
+#pragma unroll
+            for (int u = 0; u < UNROLL; ++u) v[u] = __ldg(ow.src_local + o[u]);
+#pragma unroll
+            for (int u = 0; u < UNROLL; ++u) resp[i + u * gstride] = v[u];
+        }
+        for (; i < cnt; i += gstride) resp[i] = __ldg(ow.src_local + __ldcs(queue + i));
+    }
+}
+
+// ---- K3 -----------------------------------------------------------------------------------
+template<class U>
+__global__ void __launch_bounds__(kGxThreads) gx_place_kernel(gx_requester_t<U> rq) {
+    __shared__ unsigned s_start[kGxMaxParts + 1], s_gbase[kGxMaxParts];
+    const int tid      = threadIdx.x;
+    const int nown     = rq.nowners;
+    const size_t tiles = (rq.n + kGxTile - 1) / kGxTile;
+    for (size_t t = blockIdx.x; t < tiles; t += gridDim.x) {
+        if (tid == 0) {
+            unsigned acc = 0;
+            for (int o = 0; o < nown; ++o) {
+                s_start[o] = acc;
+                s_gbase[o] = rq.tile_base[t * nown + o];
+                acc += rq.tile_cnt[t * nown + o];
+            }
+            s_start[nown] = acc;
+        }
+        __syncthreads();
+        const size_t tbase   = t * kGxTile;
+        const unsigned total = s_start[nown];
+        U v[kGxPerThread];
+        unsigned short p[kGxPerThread];
+#pragma unroll
+        for (int k = 0; k < kGxPerThread; ++k) {
+            const unsigned i = unsigned(k) * kGxThreads + tid;
+            if (i < total) {
+                int o = 0;
+                while (i >= s_start[o + 1]) ++o;
+                v[k] = __ldcs(rq.resp[o] + s_gbase[o] + (i - s_start[o]));
+                p[k] = __ldcs(rq.pos + tbase + i);
+            }
+        }
+#pragma unroll
+        for (int k = 0; k < kGxPerThread; ++k) {
+            const unsigned i = unsigned(k) * kGxThreads + tid;
+            if (i < total) rq.out[tbase + p[k]] = v[k];
+        }
+        __syncthreads();
+    }
+}
+
+// direct form (one partition of `out`): every thread keeps UNROLL independent loads in flight;
+// `src` is element 0 of the whole source, so cross-partition indices are peer loads
+template<class U, class I, int THREADS, int UNROLL>
+__global__ void __launch_bounds__(THREADS)
+    gather_direct_kernel(const I* __restrict__ index, size_t n, const U* __restrict__ src, U* __restrict__ out) {
+    const size_t gtid    = size_t(blockIdx.x) * THREADS + threadIdx.x;
+    const size_t gstride = size_t(gridDim.x) * THREADS;
+    size_t i             = gtid;
+    for (; i + (UNROLL - 1) * gstride < n; i += UNROLL * gstride) {
+        unsigned long long j[UNROLL];
+#pragma unroll
+        for (int u = 0; u < UNROLL; ++u) j[u] = (unsigned long long)__ldg(index + i + u * gstride);
+        U v[UNROLL];
+#pragma unroll
+        for (int u = 0; u < UNROLL; ++u) v[u] = src[j[u]];
+#pragma unroll
+        for (int u = 0; u < UNROLL; ++u) out[i + u * gstride] = v[u];
+    }
+    for (; i < n; i += gstride) out[i] = src[(unsigned long long)__ldg(index + i)];
+}
+
+}  // namespace sclx::b200

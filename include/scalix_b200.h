@@ -210,6 +210,8 @@ int sclx_b200_rt_scan_workspace(int logical, size_t tiles, void** desc, unsigned
 int sclx_b200_rt_scan_counters(int logical, void** counters);
 int sclx_b200_rt_reduce_workspace(int logical, size_t bytes, void** partials, void** ticket);
 int sclx_b200_rt_scratch(size_t bytes, void** ptr); /* small peer-visible scratch */
+/* per-device peer-visible grow-only workspace of sclx::algorithm::gather (exchange form) */
+int sclx_b200_rt_exchange_workspace(int logical, size_t bytes, void** ptr);
 
 /* number of kernels this library has launched in this process (monotonic) */
 unsigned long long sclx_b200_launch_count(void);

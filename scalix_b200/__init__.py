@@ -85,6 +85,7 @@ ABI = {
     "sclx_b200_rt_scan_counters": (_i, [_i, _pp]),
     "sclx_b200_rt_reduce_workspace": (_i, [_i, _sz, _pp, _pp]),
     "sclx_b200_rt_scratch": (_i, [_sz, _pp]),
+    "sclx_b200_rt_exchange_workspace": (_i, [_i, _sz, _pp]),
 }
 for _name, (_res, _args) in ABI.items():
     _fn = getattr(lib, _name)  # AttributeError here = header and library disagree

@@ -111,6 +111,7 @@ struct logical_device {
     // algorithm workspaces
     void* scan_desc = nullptr; size_t scan_bytes = 0; unsigned scan_epoch = 0;
     void* partials = nullptr; size_t partial_bytes = 0; unsigned* ticket = nullptr;
+    void* exchange = nullptr; size_t exchange_bytes = 0;  // peer-visible gather-exchange buffers
 };
 
 struct runtime {
@@ -796,6 +797,29 @@ int sclx_b200_rt_scratch(size_t bytes, void** ptr) {
         g_rt.scratch_bytes = want;
     }
     *ptr = g_rt.scratch;
+    return 0;
+}
+
+// per-device, peer-visible, grow-only workspace of the exchange gather (request queues,
+// response buffers, tile bookkeeping): a single-partition VMM array on `logical`
+int sclx_b200_rt_exchange_workspace(int logical, size_t bytes, void** ptr) {
+    if (int rc = ensure_init()) return rc;
+    if (logical < 0 || logical >= (int)g_rt.dev.size()) return fail(SCLX_E_INVALID_ARGUMENT, "bad device");
+    std::lock_guard<std::recursive_mutex> lock(g_rt.mu);
+    logical_device& ld = g_rt.dev[logical];
+    if (ld.exchange_bytes < bytes) {
+        if (ld.exchange) {
+            sync_all_streams();
+            sclx_b200_array_free(ld.exchange);
+            ld.exchange = nullptr;
+            ld.exchange_bytes = 0;
+        }
+        size_t z = 0;
+        size_t want = bytes + bytes / 8 + (size_t(1) << 21);
+        if (int rc = sclx_b200_array_create(want, 1, &logical, &z, &ld.exchange)) return rc;
+        ld.exchange_bytes = want;
+    }
+    *ptr = ld.exchange;
     return 0;
 }
 

@@ -30,6 +30,10 @@ CASES = {  # name -> (n, dtype, float tolerance or None)
     "gather_f32": (300_007, np.float32, None),
     "fill_iota": (1 << 16, np.int32, None),
     "serialize": (12 * 40_001, np.int32, None),
+    # sclx::algorithm::gather (extension): exchange form whenever there is more than one partition
+    "gather_x_f32": (300_007, np.float32, None),
+    "gather_x_f64": (150_001, np.float64, None),
+    "gather_x_skew": (300_007, np.float32, None),
 }
 
 
@@ -47,6 +51,8 @@ def run_dump(binary, case, n, path, emulate=None, real_devices=1):
     if emulate:
         env["SCLX_B200_EMULATE_DEVICES"] = str(emulate)
     env["CUDA_VISIBLE_DEVICES"] = ",".join(str(i) for i in range(real_devices))
+    if case.startswith("gather_x") and (emulate or real_devices > 1):
+        env["SCLX_GATHER_MODE"] = "exchange"
     p = subprocess.run([binary, "dump", case, str(n), path], capture_output=True, text=True, timeout=600, env=env)
     assert p.returncode == 0, f"{os.path.basename(binary)} {case}: rc={p.returncode}\n{p.stdout}\n{p.stderr}"
 
@@ -65,6 +71,11 @@ def oracle_expected(oracle, case, n):
         return oracle.axpy_f32(-0.75, oracle.symmetric_f32(n, 3), oracle.symmetric_f32(n, 4))
     if case == "gather_f32":
         return oracle.gather(oracle.uniform_f32(4 * n, 0xABC), oracle.index_u64(n, 0x6A7, 4 * n))
+    if case.startswith("gather_x"):
+        dt = np.float64 if case.endswith("f64") else np.float32
+        src = oracle.uniform_f32(4 * n, 0xABC).astype(dt) + (np.arange(4 * n, dtype=np.uint64) >> np.uint64(20)).astype(dt)
+        modulus = n // 2 if case.endswith("skew") else 4 * n
+        return oracle.gather(src, oracle.index_u64(n, 0x6A7, modulus))
     if case == "rld_u32max":
         col = np.array([oracle.lib.oracle_splitmix64(j, 7) % 1000003 for j in range(n)], dtype=np.uint64)
         return (int(col.max()) + np.tile(np.arange(3, dtype=np.uint32), 9)).astype(np.uint32)

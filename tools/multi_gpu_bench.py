@@ -28,12 +28,15 @@ def cases(n_gpus, scale):
         ("rld_f32", (n_gpus << 24) // s, 4 * 64 * ((n_gpus << 24) // s), "config 2: [64, N*2^24] f32 sum (weak)"),
         ("scan_i64", (n_gpus << 29) // s, 16 * ((n_gpus << 29) // s), "config 5 share: N*2^29 int64 (weak)"),
         ("scan_i32", (1 << 24), 8 * (1 << 24), "config 1: 2^24 int32 (latency bound)"),
-        ("gather_f32", (1 << 28) // s, 16 * ((1 << 28) // s), "config 4: 2^28 random indices into 2^30 f32"),
+        ("gather_f32", (1 << 28) // s, 16 * ((1 << 28) // s), "config 4: 2^28 random indices into 2^30 f32, user lambda (peer loads)"),
+        ("gather_x_f32", (1 << 28) // s, 16 * ((1 << 28) // s),
+         "config 4 through sclx::algorithm::gather (exchange form when N>1; the reference build runs the lambda)"),
     ]
 
 
-def run(binary, case, n, steps, warmup, n_gpus, timeout):
+def run(binary, case, n, steps, warmup, n_gpus, timeout, extra_env=None):
     env = dict(os.environ)
+    env.update(extra_env or {})
     env["CUDA_VISIBLE_DEVICES"] = ",".join(str(i) for i in range(n_gpus))
     env.pop("SCLX_B200_EMULATE_DEVICES", None)
     try:
@@ -56,11 +59,21 @@ def main():
     ap.add_argument("--skip-ref", action="store_true")
     ap.add_argument("--ref-timeout", type=int, default=240)
     ap.add_argument("--out", default=None)
+    ap.add_argument("--only", default=None, help="comma-separated case names")
     args = ap.parse_args()
     table = {"n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup, "timing": "wall clock around the blocking public API call",
              "cases": {}}
     for name, n, nbytes, note in cases(args.gpus, args.scale):
+        if args.only and name not in args.only.split(","):
+            continue
         row = {"n": n, "algorithmic_bytes": nbytes, "note": note}
+        if name == "gather_x_f32":
+            r = run(OURS, name, n, args.steps, args.warmup, args.gpus, 600, {"SCLX_GATHER_MODE": "direct"})
+            if "ms_per_step" in r:
+                r["GB/s"] = round(nbytes / (r["ms_per_step"] * 1e-3) / 1e9, 1)
+                r["Ggathers/s"] = round(n / (r["ms_per_step"] * 1e-3) / 1e9, 2)
+            row["ours_direct_kernel"] = r
+            print(name, "ours_direct_kernel", json.dumps(r), flush=True)
         for tag, binary, tmo in (("ours", OURS, 600), ("reference_um", REF, args.ref_timeout)):
             if tag == "reference_um" and (args.skip_ref or not os.path.exists(binary)):
                 continue
@@ -68,6 +81,8 @@ def main():
             if "ms_per_step" in r:
                 r["GB/s"] = round(nbytes / (r["ms_per_step"] * 1e-3) / 1e9, 1)
                 r["GB/s_per_gpu"] = round(r["GB/s"] / args.gpus, 1)
+                if name.startswith("gather"):
+                    r["Ggathers/s"] = round(n / (r["ms_per_step"] * 1e-3) / 1e9, 2)
             row[tag] = r
             print(name, tag, json.dumps(r), flush=True)
         table["cases"][name] = row
