@@ -60,6 +60,7 @@ def main():
     ap.add_argument("--ref-timeout", type=int, default=240)
     ap.add_argument("--out", default=None)
     ap.add_argument("--only", default=None, help="comma-separated case names")
+    ap.add_argument("--ref-cases", default=None, help="comma-separated cases the reference build runs (default all)")
     args = ap.parse_args()
     table = {"n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup, "timing": "wall clock around the blocking public API call",
              "cases": {}}
@@ -76,6 +77,8 @@ def main():
             print(name, "ours_direct_kernel", json.dumps(r), flush=True)
         for tag, binary, tmo in (("ours", OURS, 600), ("reference_um", REF, args.ref_timeout)):
             if tag == "reference_um" and (args.skip_ref or not os.path.exists(binary)):
+                continue
+            if tag == "reference_um" and args.ref_cases and name not in args.ref_cases.split(","):
                 continue
             r = run(binary, name, n, args.steps, args.warmup, args.gpus, tmo)
             if "ms_per_step" in r:
