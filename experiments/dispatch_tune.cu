@@ -1,0 +1,92 @@
+// Experiment: does any launch geometry lift the opaque-lambda axpy above the 2-loads-per-thread
+// latency bound?  The functor mimics a captured-by-value lambda over two arrays
+// (plain, possibly aliasing pointers).
+#include <cstdio>
+#include <cstdlib>
+#include <cuda_runtime.h>
+#define CK(x) do { cudaError_t e__ = (x); if (e__ != cudaSuccess) { printf("FAIL %s: %s\n", #x, cudaGetErrorString(e__)); exit(2); } } while (0)
+struct axpy_t { const float* x; float* y; float a; __device__ void operator()(size_t i) const { y[i] = a * x[i] + y[i]; } };
+struct axpy_ldg_t { const float* x; float* y; float a; __device__ void operator()(size_t i) const { y[i] = a * __ldg(x + i) + y[i]; } };
+
+template<class F> __global__ void persistent(F f, size_t n) {
+    size_t i = size_t(blockIdx.x) * blockDim.x + threadIdx.x, stride = size_t(gridDim.x) * blockDim.x;
+    for (; i < n; i += stride) f(i);
+}
+template<class F, int U> __global__ void persistent_unrolled(F f, size_t n) {
+    size_t i = size_t(blockIdx.x) * blockDim.x + threadIdx.x, stride = size_t(gridDim.x) * blockDim.x;
+    for (; i + (U - 1) * stride < n; i += U * stride) {
+#pragma unroll
+        for (int u = 0; u < U; ++u) f(i + u * stride);
+    }
+    for (; i < n; i += stride) f(i);
+}
+template<class F> __global__ void one_per_thread(F f, size_t n) {
+    size_t i = size_t(blockIdx.x) * blockDim.x + threadIdx.x;
+    if (i < n) f(i);
+}
+template<class F, int K> __global__ void chunked(F f, size_t n) {  // CTA owns K*blockDim contiguous elements per trip
+    const size_t chunk = size_t(K) * blockDim.x;
+    for (size_t base = size_t(blockIdx.x) * chunk; base < n; base += size_t(gridDim.x) * chunk)
+#pragma unroll
+        for (int k = 0; k < K; ++k) { size_t i = base + size_t(k) * blockDim.x + threadIdx.x; if (i < n) f(i); }
+}
+// hand-vectorised reference for the access pattern itself: 128-bit accesses, U independent
+// loads per array in flight, no aliasing
+template<int U> __global__ void axpy_vec4(const float4* __restrict__ x, float4* __restrict__ y, float a, size_t n4) {
+    size_t i = size_t(blockIdx.x) * blockDim.x + threadIdx.x, stride = size_t(gridDim.x) * blockDim.x;
+    for (; i + (U - 1) * stride < n4; i += U * stride) {
+        float4 xv[U], yv[U];
+#pragma unroll
+        for (int u = 0; u < U; ++u) { xv[u] = x[i + u * stride]; yv[u] = y[i + u * stride]; }
+#pragma unroll
+        for (int u = 0; u < U; ++u) {
+            yv[u].x = a * xv[u].x + yv[u].x; yv[u].y = a * xv[u].y + yv[u].y;
+            yv[u].z = a * xv[u].z + yv[u].z; yv[u].w = a * xv[u].w + yv[u].w;
+            y[i + u * stride] = yv[u];
+        }
+    }
+}
+template<int U> __global__ void axpy_scalar_restrict(const float* __restrict__ x, float* __restrict__ y, float a, size_t n) {
+    size_t i = size_t(blockIdx.x) * blockDim.x + threadIdx.x, stride = size_t(gridDim.x) * blockDim.x;
+    for (; i + (U - 1) * stride < n; i += U * stride) {
+        float xv[U], yv[U];
+#pragma unroll
+        for (int u = 0; u < U; ++u) { xv[u] = x[i + u * stride]; yv[u] = y[i + u * stride]; }
+#pragma unroll
+        for (int u = 0; u < U; ++u) y[i + u * stride] = a * xv[u] + yv[u];
+    }
+}
+template<class L> void timeit(const char* name, size_t n, L launch) {
+    cudaEvent_t s, e; cudaEventCreate(&s); cudaEventCreate(&e);
+    launch(); launch(); CK(cudaDeviceSynchronize());
+    cudaEventRecord(s); for (int r = 0; r < 5; ++r) launch(); cudaEventRecord(e); CK(cudaEventSynchronize(e));
+    float ms; cudaEventElapsedTime(&ms, s, e); ms /= 5;
+    printf("%-34s %8.3f ms  %8.1f GB/s\n", name, ms, 12.0 * n / ms / 1e6); fflush(stdout);
+}
+int main() {
+    const size_t n = size_t(1) << 30;
+    float *x, *y; CK(cudaMalloc(&x, n * 4)); CK(cudaMalloc(&y, n * 4)); CK(cudaMemset(x, 0, n * 4)); CK(cudaMemset(y, 0, n * 4));
+    axpy_t f{x, y, 1.5f}; axpy_ldg_t g{x, y, 1.5f};
+    const int sms = 148;
+    for (int block : {128, 256, 512, 1024}) {
+        int per_sm = 2048 / block; char name[96];
+        snprintf(name, sizeof name, "persistent block=%d grid=%d", block, sms * per_sm);
+        timeit(name, n, [&] { persistent<<<sms * per_sm, block>>>(f, n); });
+        snprintf(name, sizeof name, "persistent block=%d grid=2x", block);
+        timeit(name, n, [&] { persistent<<<sms * per_sm * 2, block>>>(f, n); });
+    }
+    timeit("one_per_thread block=256", n, [&] { one_per_thread<<<unsigned((n + 255) / 256), 256>>>(f, n); });
+    timeit("one_per_thread block=1024", n, [&] { one_per_thread<<<unsigned((n + 1023) / 1024), 1024>>>(f, n); });
+    timeit("unrolled x4 (aliasing, expect same)", n, [&] { persistent_unrolled<axpy_t, 4><<<sms * 8, 256>>>(f, n); });
+    timeit("unrolled x4 with __ldg(x)", n, [&] { persistent_unrolled<axpy_ldg_t, 4><<<sms * 8, 256>>>(g, n); });
+    timeit("persistent with __ldg(x)", n, [&] { persistent<<<sms * 8, 256>>>(g, n); });
+    timeit("chunked K=4 block=256", n, [&] { chunked<axpy_t, 4><<<sms * 8, 256>>>(f, n); });
+    timeit("chunked K=8 block=256", n, [&] { chunked<axpy_t, 8><<<sms * 8, 256>>>(f, n); });
+    timeit("hand float4 U=1", n, [&] { axpy_vec4<1><<<sms * 8, 256>>>((const float4*)x, (float4*)y, 1.5f, n / 4); });
+    timeit("hand float4 U=2", n, [&] { axpy_vec4<2><<<sms * 8, 256>>>((const float4*)x, (float4*)y, 1.5f, n / 4); });
+    timeit("hand float4 U=4", n, [&] { axpy_vec4<4><<<sms * 4, 256>>>((const float4*)x, (float4*)y, 1.5f, n / 4); });
+    timeit("hand scalar restrict U=2", n, [&] { axpy_scalar_restrict<2><<<sms * 8, 256>>>(x, y, 1.5f, n); });
+    timeit("hand scalar restrict U=4", n, [&] { axpy_scalar_restrict<4><<<sms * 8, 256>>>(x, y, 1.5f, n); });
+    timeit("hand scalar restrict U=8", n, [&] { axpy_scalar_restrict<8><<<sms * 8, 256>>>(x, y, 1.5f, n); });
+    return 0;
+}

@@ -414,7 +414,7 @@ def test_scan_config5_full_size_closed_form(sclx):
     carry-seeded single-pass scans), on one GPU (32 GiB in + 32 GiB out).  Input iota(0), so
     out[i] = i(i+1)/2 mod 2^64: checked at the last element, in windows around every partition
     boundary, and through a checksum of the whole output (our reduce kernel, mod 2^64)
-    = n(n+1)(n+2)/6.  The reference itself cannot run this size on one device (32-bit thread
+    = (n-1)n(n+1)/6.  The reference itself cannot run this size on one device (32-bit thread
     arithmetic, scalix/kernel_info.cuh:86-101)."""
     n, ndev, item = 1 << 32, 8, 8
     d_in, d_out = sclx.DeviceBuffer(n * item), sclx.DeviceBuffer(n * item)
@@ -441,9 +441,9 @@ def test_scan_config5_full_size_closed_form(sclx):
         assert np.array_equal(got, want), f"window at {s}"
     chk = sclx.DeviceBuffer(16)
     sclx.reduce(d_out, n, sclx.U64, sclx.PLUS, 0, chk.ptr)
-    assert int(chk.to_numpy(np.uint64)[0]) == (n * (n + 1) * (n + 2) // 6) & m64
+    assert int(chk.to_numpy(np.uint64)[0]) == ((n - 1) * n * (n + 1) // 6) & m64
     # the single-partition (pure single-pass) scan of the same input must give the same checksum
     sclx.inclusive_scan(d_in, d_out, n, sclx.I64, sclx.PLUS)
     sclx.reduce(d_out, n, sclx.U64, sclx.PLUS, 0, chk.ptr)
-    assert int(chk.to_numpy(np.uint64)[0]) == (n * (n + 1) * (n + 2) // 6) & m64
+    assert int(chk.to_numpy(np.uint64)[0]) == ((n - 1) * n * (n + 1) // 6) & m64
     assert int(d_out.to_numpy(np.uint64, count=1, offset_bytes=(n - 1) * item)[0]) == closed(n - 1)
