@@ -20,16 +20,21 @@ FLAGS = ["-std=c++17", "-O3", "-gencode", "arch=compute_100a,code=sm_100a", "-li
          "-L", LIBDIR, "-lscalix_b200", "-Xlinker", "-rpath", "-Xlinker", "$ORIGIN/../../scalix_b200/lib"]
 
 
-def newest_header():
-    newest = 0.0
-    for root, _, files in os.walk(os.path.join(REPO, "include")):
-        for f in files:
-            newest = max(newest, os.path.getmtime(os.path.join(root, f)))
+def newest_dependency(src, extra):
+    """mtime of the newest repository file `src` includes (nvcc -M; seconds), so touching a header
+    only rebuilds the programs that include it — examples/inclusive_scan.cu takes ten minutes"""
+    p = subprocess.run(["nvcc", *FLAGS[:FLAGS.index("-L")], *extra, "-M", src], capture_output=True, text=True)
+    newest = os.path.getmtime(src)
+    if p.returncode != 0:
+        return float("inf")
+    for tok in p.stdout.replace("\\\n", " ").split():
+        if tok.startswith(REPO) and os.path.exists(tok):
+            newest = max(newest, os.path.getmtime(tok))
     return newest
 
 
 def build_one(src, out, extra=()):
-    if os.path.exists(out) and os.path.getmtime(out) >= max(os.path.getmtime(src), newest_header()):
+    if os.path.exists(out) and os.path.getmtime(out) >= newest_dependency(src, extra):
         return out, 0, ""
     p = subprocess.run(["nvcc", *FLAGS, *extra, "-o", out, src], capture_output=True, text=True)
     return out, p.returncode, p.stdout + p.stderr

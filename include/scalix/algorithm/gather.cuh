@@ -42,10 +42,13 @@ struct gather_carrier<8> {
 inline size_t gx_align(size_t v) { return (v + 255) & ~size_t(255); }
 
 inline unsigned gx_capacity(size_t n_requester, int nowners) {
-    // 1.25 x the uniform share + one tile, never more than the requester's whole partition
+    // 1.25 x the uniform share + one tile (never more than the requester's whole partition),
+    // plus the padding of every tile's run to a multiple of 32 entries
     const size_t share = (n_requester + nowners - 1) / nowners;
     size_t cap         = share + share / 4 + b200::kGxTile;
     if (cap > n_requester) cap = n_requester;
+    const size_t tiles = (n_requester + b200::kGxTile - 1) / b200::kGxTile;
+    cap += tiles * 32;
     cap = (cap + 31) & ~size_t(31);
     return unsigned(cap);
 }
@@ -78,7 +81,7 @@ __host__ void gather(
     const index_t_* idx_ptr = index.data().get();
 
     bool exchange_ok = (sizeof(T) == 4 || sizeof(T) == 8) && nown > 1 && nown <= b200::kGxMaxParts
-                       && nreq <= b200::kGxMaxParts && n < (size_t(1) << 32) * size_t(nreq);
+                       && nreq <= b200::kGxMaxParts && n < (size_t(1) << 31) * size_t(nreq);
     // owners must be uniform blocks of `per` elements starting at p*per (true for every
     // array partitioned by set_primary_devices; not for arbitrary slices), distinct devices
     size_t per = 0;

@@ -210,6 +210,14 @@ int sclx_b200_rt_scan_workspace(int logical, size_t tiles, void** desc, unsigned
 int sclx_b200_rt_scan_counters(int logical, void** counters);
 int sclx_b200_rt_reduce_workspace(int logical, size_t bytes, void** partials, void** ticket);
 int sclx_b200_rt_scratch(size_t bytes, void** ptr); /* small peer-visible scratch */
+/* Freed arrays stay mapped in a bounded pool (default 32 GiB, SCLX_B200_POOL_BYTES; 0 = off) and
+ * are reused by the next array_create with the same size and placement: building a multi-GiB
+ * peer-mapped range costs tens of milliseconds on a multi-GPU node, reusing one costs its
+ * zero-fill.  (The reference pays cudaMallocManaged + 4*ndev+2 cudaMemAdvise + ndev prefetches
+ * per array, scalix/array.cuh:345,522-612.) */
+size_t sclx_b200_rt_pool_bytes(void);
+unsigned long long sclx_b200_rt_pool_hits(void);
+int sclx_b200_rt_pool_release(void);
 /* per-device peer-visible grow-only workspace of sclx::algorithm::gather (exchange form) */
 int sclx_b200_rt_exchange_workspace(int logical, size_t bytes, void** ptr);
 

@@ -86,6 +86,9 @@ ABI = {
     "sclx_b200_rt_reduce_workspace": (_i, [_i, _sz, _pp, _pp]),
     "sclx_b200_rt_scratch": (_i, [_sz, _pp]),
     "sclx_b200_rt_exchange_workspace": (_i, [_i, _sz, _pp]),
+    "sclx_b200_rt_pool_bytes": (_sz, []),
+    "sclx_b200_rt_pool_hits": (C.c_ulonglong, []),
+    "sclx_b200_rt_pool_release": (_i, []),
 }
 for _name, (_res, _args) in ABI.items():
     _fn = getattr(lib, _name)  # AttributeError here = header and library disagree

@@ -107,6 +107,7 @@ struct logical_device {
     int physical        = 0;
     cudaStream_t stream = nullptr;
     cudaEvent_t done    = nullptr;  // recorded after the latest launch group
+    cudaEvent_t gate    = nullptr;  // recorded by the hub of a launch group once every device's `done` has fired
     int sm_count        = 0;
     // algorithm workspaces
     void* scan_desc = nullptr; size_t scan_bytes = 0; unsigned scan_epoch = 0;
@@ -128,6 +129,12 @@ struct runtime {
     struct sigaction old_action {};
     void* scratch = nullptr; size_t scratch_bytes = 0;
     unsigned long long faults = 0, flushed_chunks = 0;
+    // freed arrays kept mapped for reuse (VA + physical pages + peer access + mirror intact):
+    // creating a multi-GiB peer-mapped range costs tens of ms on a multi-GPU node, reusing one
+    // costs its zero-fill.  Oldest first; bounded by pool_cap bytes (SCLX_B200_POOL_BYTES).
+    std::vector<allocation*> pool;
+    size_t pool_bytes = 0, pool_cap = size_t(32) << 30;
+    unsigned long long pool_hits = 0, pool_misses = 0;
 };
 runtime g_rt;
 
@@ -148,6 +155,7 @@ int ensure_init() {
            && resolve("cuGetErrorString", g_drv.GetErrorString);
     if (!ok) return fail(SCLX_E_RUNTIME, "CUDA virtual memory management entry points unavailable");
     g_drv.ok = true;
+    if (const char* e = getenv("SCLX_B200_POOL_BYTES")) g_rt.pool_cap = (size_t)strtoull(e, nullptr, 10);
     if (g_rt.emulated == 0) {
         if (const char* e = getenv("SCLX_B200_EMULATE_DEVICES")) {
             int v = atoi(e);
@@ -165,6 +173,7 @@ int ensure_init() {
         RT(cudaFree(nullptr));
         RT(cudaStreamCreateWithFlags(&ld.stream, cudaStreamNonBlocking));
         RT(cudaEventCreateWithFlags(&ld.done, cudaEventDisableTiming));
+        RT(cudaEventCreateWithFlags(&ld.gate, cudaEventDisableTiming));
         RT(cudaDeviceGetAttribute(&ld.sm_count, cudaDevAttrMultiProcessorCount, ld.physical));
         RT(cudaMalloc(&ld.ticket, 256));
         RT(cudaMemset(ld.ticket, 0, 256));
@@ -456,6 +465,85 @@ int unmap_runs(allocation& al) {
     return 0;
 }
 
+// tear an allocation down completely (mappings, physical pages, mirror, reservation)
+int destroy_allocation(allocation* al) {
+    if (al->overlay_ok) {
+        // give the range back to a plain reservation before the driver unmaps it
+        mmap(al->base, al->va_bytes, PROT_NONE, MAP_PRIVATE | MAP_ANONYMOUS | MAP_FIXED | MAP_NORESERVE, -1, 0);
+        munmap(al->alias, al->va_bytes);
+        close(al->memfd);
+    }
+    int rc = unmap_runs(*al);
+    if (!rc) {
+        CUresult r = g_drv.MemAddressFree((CUdeviceptr)al->base, al->va_bytes);
+        if (r != CUDA_SUCCESS) rc = cu_fail(r, "cuMemAddressFree");
+    }
+    delete al;
+    return rc;
+}
+
+// forget every host-valid chunk WITHOUT writing anything back (the array is dead)
+void drop_mirror(allocation& al) {
+    if (!al.overlay_ok) return;
+    const size_t nchunks = al.state.size();
+    size_t c = 0;
+    while (c < nchunks) {
+        if (al.state[c] == kInvalid) { ++c; continue; }
+        size_t e = c;
+        while (e < nchunks && al.state[e] != kInvalid) ++e;
+        const size_t off = c * kMirrorChunk, len = (e - c) * kMirrorChunk;
+        mprotect(al.base + off, len, PROT_NONE);
+        if (al.memfd >= 0) fallocate(al.memfd, FALLOC_FL_PUNCH_HOLE | FALLOC_FL_KEEP_SIZE, off, len);
+        for (size_t k = c; k < e; ++k) al.state[k] = kInvalid;
+        c = e;
+    }
+    al.n_valid = 0;
+}
+
+int zero_runs(allocation& al) {
+    int cur = 0;
+    cudaGetDevice(&cur);
+    for (auto& r : al.runs) {
+        logical_device& ld = g_rt.dev[r.logical_device];
+        RT(cudaSetDevice(ld.physical));
+        RT(cudaMemsetAsync(al.base + r.offset, 0, r.bytes, ld.stream));
+    }
+    for (auto& r : al.runs) {
+        logical_device& ld = g_rt.dev[r.logical_device];
+        RT(cudaSetDevice(ld.physical));
+        RT(cudaStreamSynchronize(ld.stream));
+    }
+    RT(cudaSetDevice(cur));
+    return 0;
+}
+
+void pool_purge(size_t keep_bytes) {
+    while (!g_rt.pool.empty() && g_rt.pool_bytes > keep_bytes) {
+        allocation* al = g_rt.pool.front();
+        g_rt.pool.erase(g_rt.pool.begin());
+        g_rt.pool_bytes -= al->va_bytes;
+        destroy_allocation(al);
+    }
+}
+
+// a pooled allocation with exactly this placement, or nullptr
+allocation* pool_take(size_t va_bytes, const std::vector<allocation::run>& want) {
+    for (size_t i = g_rt.pool.size(); i-- > 0;) {
+        allocation* al = g_rt.pool[i];
+        if (al->va_bytes != va_bytes || al->runs.size() != want.size()) continue;
+        bool same = true;
+        for (size_t k = 0; same && k < want.size(); ++k)
+            same = al->runs[k].offset == want[k].offset && al->runs[k].bytes == want[k].bytes
+                && physical_of(al->runs[k].logical_device) == physical_of(want[k].logical_device);
+        if (!same) continue;
+        for (size_t k = 0; k < want.size(); ++k) al->runs[k].logical_device = want[k].logical_device;
+        g_rt.pool.erase(g_rt.pool.begin() + (long)i);
+        g_rt.pool_bytes -= al->va_bytes;
+        return al;
+    }
+    return nullptr;
+}
+
 int validate_parts(size_t bytes, int nparts, const int* devices, const size_t* starts) {
     if (nparts < 1 || !devices || !starts) return fail(SCLX_E_INVALID_ARGUMENT, "array: bad partition list");
     if (starts[0] != 0) return fail(SCLX_E_INVALID_ARGUMENT, "array: first partition must start at byte 0");
@@ -516,13 +604,33 @@ int sclx_b200_array_create(size_t bytes, int nparts, const int* devices, const s
     allocation* al  = new allocation;
     al->bytes       = bytes;
     al->va_bytes    = std::max<size_t>(g, (bytes + g - 1) / g * g);
+    build_runs(*al, nparts, devices, byte_starts);
+    if (allocation* pooled = pool_take(al->va_bytes, al->runs)) {
+        delete al;
+        pooled->bytes = bytes;
+        if (int rc = zero_runs(*pooled)) { destroy_allocation(pooled); return rc; }
+        ++g_rt.pool_hits;
+        g_rt.allocs[pooled->base] = pooled;
+        *base                     = pooled->base;
+        return 0;
+    }
+    ++g_rt.pool_misses;
     CUdeviceptr va  = 0;
     CUresult r      = g_drv.MemAddressReserve(&va, al->va_bytes, g, 0, 0);
     if (r != CUDA_SUCCESS) { delete al; return cu_fail(r, "cuMemAddressReserve"); }
     al->base = (char*)va;
-    build_runs(*al, nparts, devices, byte_starts);
-    if (int rc = map_runs(*al, true)) {
-        unmap_runs(*al);
+    int rc   = map_runs(*al, true);
+    if (rc && !g_rt.pool.empty()) {
+        // out of device memory with arrays parked in the pool: give them back and retry once
+        for (auto& rr : al->runs)
+            if (rr.handle) { g_drv.MemUnmap((CUdeviceptr)(al->base + rr.offset), rr.bytes); g_drv.MemRelease(rr.handle); rr.handle = 0; }
+        pool_purge(0);
+        rc = map_runs(*al, true);
+    }
+    if (rc) {
+        for (auto& rr : al->runs)
+            if (rr.handle) { g_drv.MemUnmap((CUdeviceptr)(al->base + rr.offset), rr.bytes); g_drv.MemRelease(rr.handle); }
+        al->runs.clear();
         g_drv.MemAddressFree(va, al->va_bytes);
         delete al;
         return rc;
@@ -545,19 +653,14 @@ int sclx_b200_array_free(void* base) {
         al->n_valid = 0;
     }
     g_rt.allocs.erase(it);
-    if (al->overlay_ok) {
-        // give the range back to a plain reservation before the driver unmaps it
-        mmap(al->base, al->va_bytes, PROT_NONE, MAP_PRIVATE | MAP_ANONYMOUS | MAP_FIXED | MAP_NORESERVE, -1, 0);
-        munmap(al->alias, al->va_bytes);
-        close(al->memfd);
+    if (g_rt.pool_cap > 0 && al->va_bytes <= g_rt.pool_cap && !al->runs.empty()) {
+        drop_mirror(*al);
+        g_rt.pool.push_back(al);
+        g_rt.pool_bytes += al->va_bytes;
+        pool_purge(g_rt.pool_cap);
+        return 0;
     }
-    int rc = unmap_runs(*al);
-    if (!rc) {
-        CUresult r = g_drv.MemAddressFree((CUdeviceptr)al->base, al->va_bytes);
-        if (r != CUDA_SUCCESS) rc = cu_fail(r, "cuMemAddressFree");
-    }
-    delete al;
-    return rc;
+    return destroy_allocation(al);
 }
 
 // move the physical pages to a new split, keeping the pointer (and the data)
@@ -665,11 +768,26 @@ int sclx_b200_rt_begin_launch(int ndev, const int* devices) {
     std::lock_guard<std::recursive_mutex> lock(g_rt.mu);
     int cur = 0;
     cudaGetDevice(&cur);
-    for (int i = 0; i < ndev; ++i) {
-        logical_device& me = g_rt.dev[devices[i]];
-        RT(cudaSetDevice(me.physical));
+    if (ndev <= 2) {
+        for (int i = 0; i < ndev; ++i) {
+            logical_device& me = g_rt.dev[devices[i]];
+            RT(cudaSetDevice(me.physical));
+            for (size_t o = 0; o < g_rt.dev.size(); ++o)
+                if ((int)o != devices[i]) RT(cudaStreamWaitEvent(me.stream, g_rt.dev[o].done, 0));
+        }
+    } else {
+        // O(N) instead of O(N^2) driver calls: the first participant (hub) waits for every
+        // other device, records its gate, the other participants wait for the gate
+        logical_device& hub = g_rt.dev[devices[0]];
+        RT(cudaSetDevice(hub.physical));
         for (size_t o = 0; o < g_rt.dev.size(); ++o)
-            if ((int)o != devices[i]) RT(cudaStreamWaitEvent(me.stream, g_rt.dev[o].done, 0));
+            if ((int)o != devices[0]) RT(cudaStreamWaitEvent(hub.stream, g_rt.dev[o].done, 0));
+        RT(cudaEventRecord(hub.gate, hub.stream));
+        for (int i = 1; i < ndev; ++i) {
+            logical_device& me = g_rt.dev[devices[i]];
+            RT(cudaSetDevice(me.physical));
+            RT(cudaStreamWaitEvent(me.stream, hub.gate, 0));
+        }
     }
     RT(cudaSetDevice(cur));
     return 0;
@@ -824,5 +942,14 @@ int sclx_b200_rt_exchange_workspace(int logical, size_t bytes, void** ptr) {
 }
 
 unsigned long long sclx_b200_rt_host_faults(void) { return g_rt.faults; }
+
+// array pool: bytes parked / reuse counters / explicit release (e.g. before a large cudaMalloc)
+size_t sclx_b200_rt_pool_bytes(void) { return g_rt.pool_bytes; }
+unsigned long long sclx_b200_rt_pool_hits(void) { return g_rt.pool_hits; }
+int sclx_b200_rt_pool_release(void) {
+    std::lock_guard<std::recursive_mutex> lock(g_rt.mu);
+    pool_purge(0);
+    return 0;
+}
 
 }  // extern "C"

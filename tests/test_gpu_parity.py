@@ -447,3 +447,36 @@ def test_scan_config5_full_size_closed_form(sclx):
     sclx.reduce(d_out, n, sclx.U64, sclx.PLUS, 0, chk.ptr)
     assert int(chk.to_numpy(np.uint64)[0]) == ((n - 1) * n * (n + 1) // 6) & m64
     assert int(d_out.to_numpy(np.uint64, count=1, offset_bytes=(n - 1) * item)[0]) == closed(n - 1)
+
+
+# ----------------------------------------------------------------------------- array pool (memory manager)
+def test_array_pool_reuses_a_freed_range_zero_filled(sclx):
+    """a freed array stays mapped in the pool; the next array with the same size and placement
+    reuses it and must come back zero-filled (fresh managed memory is zero in the reference,
+    examples/distributed_indexing.cu:79 relies on it)"""
+    lib = sclx.lib
+    sclx.check(lib.sclx_b200_rt_init())
+    nbytes = 8 << 20
+    dev0, zero = C.c_int(0), C.c_size_t(0)
+
+    class Raw:
+        def __init__(self, ptr):
+            self.ptr = ptr
+
+    base = C.c_void_p()
+    sclx.check(lib.sclx_b200_array_create(nbytes, 1, C.byref(dev0), C.byref(zero), C.byref(base)))
+    sclx.fill(Raw(base.value), nbytes // 4, 0xDEADBEEF, np.uint32)
+    sclx.synchronize()
+    first = base.value
+    sclx.check(lib.sclx_b200_array_free(base))
+    assert lib.sclx_b200_rt_pool_bytes() >= nbytes
+    hits = lib.sclx_b200_rt_pool_hits()
+    sclx.check(lib.sclx_b200_array_create(nbytes, 1, C.byref(dev0), C.byref(zero), C.byref(base)))
+    assert lib.sclx_b200_rt_pool_hits() == hits + 1 and base.value == first
+    got = np.empty(nbytes // 4, np.uint32)
+    sclx.check(lib.sclx_b200_memcpy_d2h(got.ctypes.data, base.value, nbytes, None))
+    sclx.synchronize()
+    assert not got.any()
+    sclx.check(lib.sclx_b200_array_free(base))
+    sclx.check(lib.sclx_b200_rt_pool_release())
+    assert lib.sclx_b200_rt_pool_bytes() == 0
