@@ -399,7 +399,7 @@ def run_ours(args):
             },
             "roofline": {"bound": "hbm", "achieved": round(achieved, 1), "peak": peak, "unit": "GB/s",
                          "frac": round(achieved / peak, 4), "traffic": None,
-                         "kernel": "reduce_last_dim_kernel<float, op_plus, 256, 8, 4>",
+                         "kernel": "reduce_last_dim_kernel<float, op_plus, 256, 16, 4, 2>",
                          "kernel_ms": round(kernel_ms, 4)},
             "e2e": {"value": round(e2e_value, 2), "unit": UNIT, "h2d_bytes_per_step": nbytes,
                     "d2h_bytes_per_step": ROWS * 4, "ms_per_step": round(e2e_s / e2e_steps * 1e3, 3)},

@@ -75,6 +75,10 @@ int main() {
         snprintf(name, sizeof name, "persistent block=%d grid=2x", block);
         timeit(name, n, [&] { persistent<<<sms * per_sm * 2, block>>>(f, n); });
     }
+    for (int mult : {4, 8, 16, 64, 256}) {
+        char name[96]; snprintf(name, sizeof name, "persistent block=256 grid=%dx", mult);
+        timeit(name, n, [&] { persistent<<<sms * 8 * mult, 256>>>(f, n); });
+    }
     timeit("one_per_thread block=256", n, [&] { one_per_thread<<<unsigned((n + 255) / 256), 256>>>(f, n); });
     timeit("one_per_thread block=1024", n, [&] { one_per_thread<<<unsigned((n + 1023) / 1024), 1024>>>(f, n); });
     timeit("unrolled x4 (aliasing, expect same)", n, [&] { persistent_unrolled<axpy_t, 4><<<sms * 8, 256>>>(f, n); });

@@ -123,9 +123,10 @@ __host__ void gather(
         if (!use_exchange) {
             b200::for_each_partition(out, out_info, [&](const b200::partition_t& p) {
                 if (p.elements == 0) return;
-                const size_t work = (p.elements + 255) / 256;
-                b200::gather_direct_kernel<U, index_t_, 256, 8>
-                    <<<b200::persistent_grid(work, 8, b200::sm_count_of(p.device)), 256, 0, p.stream>>>(
+                // one 1024-index chunk per CTA: random-access kernels run faster de-synchronised
+                const size_t work = std::min<size_t>((p.elements + 1023) / 1024, size_t(0x7fffffff));
+                b200::gather_direct_kernel<U, index_t_, 256, 4>
+                    <<<unsigned(work), 256, 0, p.stream>>>(
                         idx_ptr + p.offset, p.elements, src_base, out_base + p.offset
                     );
             });
@@ -225,14 +226,17 @@ __host__ void gather(
                     <<<grid, b200::kGxThreads, 0, p.stream>>>(x, idx_ptr + p.offset);
             });
             b200::for_each_partition(src, src_info, [&](const b200::partition_t& p) {
-                b200::gx_serve_kernel<U, 256, 4>
-                    <<<unsigned(b200::sm_count_of(p.device)) * 8u, 256, 0, p.stream>>>(ow[p.ordinal]);
+                unsigned max_cap = 0;
+                for (int r = 0; r < nreq; ++r) max_cap = std::max(max_cap, cap[r][p.ordinal]);
+                if (max_cap == 0) return;
+                const dim3 grid((max_cap + b200::kGxServeChunk - 1) / b200::kGxServeChunk, unsigned(nreq));
+                b200::gx_serve_kernel<U><<<grid, b200::kGxServeThreads, 0, p.stream>>>(ow[p.ordinal]);
             });
             b200::for_each_partition(out, out_info, [&](const b200::partition_t& p) {
                 const auto& x = rq[p.ordinal];
                 if (x.n == 0) return;
                 const unsigned grid
-                    = b200::persistent_grid(tiles_r[p.ordinal], 4, b200::sm_count_of(p.device));
+                    = b200::persistent_grid(tiles_r[p.ordinal], 3, b200::sm_count_of(p.device));
                 b200::gx_place_kernel<U><<<grid, b200::kGxThreads, 0, p.stream>>>(x);
             });
         }

@@ -8,9 +8,9 @@
 //   * all linear arithmetic is 64-bit (no wrap at 2^32 elements per device);
 //   * the md-index is advanced incrementally with carry propagation instead of being
 //     rebuilt with (Rank-1) 64-bit div+mod per element per trip;
-//   * the grid is sized to the machine (persistent CTAs, multiples of the SM count) and
-//     the loop strides by the whole grid, so consecutive threads touch consecutive
-//     elements (coalesced) on every trip.
+//   * the grid is sized to the machine (a fixed number of resident waves, multiples of the
+//     SM count: launch_config.cuh) and the loop strides by the whole grid, so consecutive
+//     threads touch consecutive elements (coalesced) on every trip.
 #pragma once
 
 #include "../../kernel_info.cuh"

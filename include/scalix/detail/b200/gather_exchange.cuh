@@ -88,51 +88,58 @@ struct gx_owner_t {
 };
 
 // ---- K1 -----------------------------------------------------------------------------------
+// Per-thread state is packed (32-bit offset + owner<<16|rank) so three 512-thread CTAs fit an
+// SM; the first version kept the 64-bit indices live, needed 58 registers, ran two CTAs per SM
+// and was issue-bound at 1.0 ms for 2^27 indices (profiles/r01_ncu_gather_exchange_details.txt).
 template<class U, class I>
-__global__ void __launch_bounds__(kGxThreads)
+__global__ void __launch_bounds__(kGxThreads, 3)
     gx_partition_kernel(gx_requester_t<U> rq, const I* __restrict__ index) {
     __shared__ unsigned s_off[kGxTile];
     __shared__ unsigned short s_pos[kGxTile];
     __shared__ unsigned s_cnt[kGxMaxParts], s_start[kGxMaxParts + 1], s_gbase[kGxMaxParts],
         s_take[kGxMaxParts];
-    const int tid        = threadIdx.x;
+    const unsigned tid   = threadIdx.x;
     const unsigned lane  = tid & 31;
     const unsigned below = (1u << lane) - 1u;
     const int nown       = rq.nowners;
     const size_t tiles   = (rq.n + kGxTile - 1) / kGxTile;
 
     for (size_t t = blockIdx.x; t < tiles; t += gridDim.x) {
-        if (tid < nown) s_cnt[tid] = 0;
+        if (tid < unsigned(nown)) s_cnt[tid] = 0;
         __syncthreads();
-        const size_t tbase = t * kGxTile;
-        unsigned long long e[kGxPerThread];
-        unsigned q[kGxPerThread], off[kGxPerThread], rank[kGxPerThread];
+        const size_t tbase   = t * kGxTile;
+        const unsigned avail = unsigned(rq.n - tbase < size_t(kGxTile) ? rq.n - tbase : size_t(kGxTile));
+        const I* __restrict__ tile_index = index + tbase;
+        unsigned off[kGxPerThread], qr[kGxPerThread];  // qr = owner << 16 | rank in (tile, owner)
+        {
+            unsigned long long e[kGxPerThread];
 #pragma unroll
-        for (int k = 0; k < kGxPerThread; ++k) {
-            const size_t j = tbase + size_t(k) * kGxThreads + tid;
-            e[k]           = j < rq.n ? (unsigned long long)__ldg(index + j) : ~0ull;
-        }
-#pragma unroll
-        for (int k = 0; k < kGxPerThread; ++k) {
-            const bool valid = tbase + size_t(k) * kGxThreads + tid < rq.n;
-            q[k] = 0xffffffffu, off[k] = 0;
-            if (valid) {
-                gx_owner(e[k], rq.div, q[k], off[k]);
-                if (q[k] >= unsigned(nown)) q[k] = unsigned(nown) - 1;  // out of range: UB upstream too
+            for (int k = 0; k < kGxPerThread; ++k) {
+                const unsigned j = unsigned(k) * kGxThreads + tid;
+                e[k]             = j < avail ? (unsigned long long)__ldg(tile_index + j) : ~0ull;
             }
-            // one shared-memory atomic per (warp, owner)
-            const unsigned peers = __match_any_sync(0xffffffffu, q[k]);
-            const int leader     = __ffs(peers) - 1;
-            unsigned first       = 0;
-            if (int(lane) == leader && valid) first = atomicAdd(&s_cnt[q[k]], unsigned(__popc(peers)));
-            first   = __shfl_sync(0xffffffffu, first, leader);
-            rank[k] = first + unsigned(__popc(peers & below));
+#pragma unroll
+            for (int k = 0; k < kGxPerThread; ++k) {
+                const bool valid = unsigned(k) * kGxThreads + tid < avail;
+                unsigned q       = 0xffu;
+                off[k]           = 0;
+                if (valid) {
+                    gx_owner(e[k], rq.div, q, off[k]);
+                    if (q >= unsigned(nown)) q = unsigned(nown) - 1;  // out of range: UB upstream too
+                }
+                // one shared-memory atomic per (warp, owner)
+                const unsigned peers = __match_any_sync(0xffffffffu, q);
+                const int leader     = __ffs(peers) - 1;
+                unsigned first       = 0;
+                if (int(lane) == leader && valid) first = atomicAdd(&s_cnt[q], unsigned(__popc(peers)));
+                first = __shfl_sync(0xffffffffu, first, leader);
+                qr[k] = (q << 16) | (first + unsigned(__popc(peers & below)));
+            }
         }
         __syncthreads();
-        if (tid < nown) {
+        if (tid < unsigned(nown)) {
             // runs are reserved in multiples of 32 entries, so every run starts on a 128-byte
-            // line of the queue and a warp's store of 32 offsets is ONE full-line NVLink write
-            // (misaligned runs went out as 32-byte packets: 46 % protocol overhead in ncu)
+            // line of the queue and a warp's store of 32 offsets is one full-line NVLink write
             const unsigned c    = s_cnt[tid];
             const unsigned g    = c ? atomicAdd(&rq.counters[tid], (c + 31u) & ~31u) : 0u;
             const unsigned room = g < rq.cap[tid] ? rq.cap[tid] - g : 0u;
@@ -154,14 +161,16 @@ __global__ void __launch_bounds__(kGxThreads)
         __syncthreads();
 #pragma unroll
         for (int k = 0; k < kGxPerThread; ++k) {
-            const size_t j = tbase + size_t(k) * kGxThreads + tid;
-            if (j < rq.n) {
-                if (rank[k] < s_take[q[k]]) {
-                    const unsigned slot = s_start[q[k]] + rank[k];
+            const unsigned j = unsigned(k) * kGxThreads + tid;
+            if (j < avail) {
+                const unsigned q = qr[k] >> 16, rank = qr[k] & 0xffffu;
+                if (rank < s_take[q]) {
+                    const unsigned slot = s_start[q] + rank;
                     s_off[slot]         = off[k];
-                    s_pos[slot]         = (unsigned short)(k * kGxThreads + tid);
+                    s_pos[slot]         = (unsigned short)j;
                 } else {
-                    rq.out[j] = rq.src_base[e[k]];  // queue full: direct (peer) load
+                    // queue full: direct (peer) load
+                    rq.out[tbase + j] = rq.src_base[(unsigned long long)__ldg(tile_index + j)];
                 }
             }
         }
@@ -179,27 +188,54 @@ __global__ void __launch_bounds__(kGxThreads)
 }
 
 // ---- K2 -----------------------------------------------------------------------------------
-template<class U, int THREADS, int UNROLL>
-__global__ void __launch_bounds__(THREADS) gx_serve_kernel(gx_owner_t<U> ow) {
-    const size_t gtid    = size_t(blockIdx.x) * THREADS + threadIdx.x;
-    const size_t gstride = size_t(gridDim.x) * THREADS;
-    for (int r = 0; r < ow.nreq; ++r) {
-        unsigned cnt = __ldcg(ow.counter[r]);
-        if (cnt > ow.cap[r]) cnt = ow.cap[r];
-        const unsigned* __restrict__ queue = ow.queue[r];
-        U* __restrict__ resp               = ow.resp[r];
-        size_t i                           = gtid;
-        for (; i + (UNROLL - 1) * gstride < cnt; i += UNROLL * gstride) {
-            unsigned o[UNROLL];
+// One random 4/8-byte load per entry: bound by the HBM's random-access rate, not by bytes.
+// experiments/serve_tune.cu (profiles/r01_serve_tune.txt): a persistent grid in lock step
+// serves 36-37 G loads/s, many small CTAs (one 1024-entry chunk each, no loop) 47-48 G/s —
+// the staggered CTA starts de-synchronise the queue-read / random-read / store phases.  The
+// L2::64B hint halves the DRAM bytes fetched per load (126 -> 63).
+template<class U>
+__device__ __forceinline__ U gx_load_random(const U* p) {
+    if constexpr (sizeof(U) == 4) {
+        unsigned v;
+        asm volatile("ld.global.nc.L2::64B.b32 %0, [%1];" : "=r"(v) : "l"(p));
+        return U(v);
+    } else if constexpr (sizeof(U) == 8) {
+        unsigned long long v;
+        asm volatile("ld.global.nc.L2::64B.b64 %0, [%1];" : "=l"(v) : "l"(p));
+        return U(v);
+    } else {
+        return *p;
+    }
+}
+
+constexpr int kGxServeThreads = 256, kGxServeUnroll = 4;
+constexpr int kGxServeChunk   = kGxServeThreads * kGxServeUnroll;
+
+// grid = (ceil(max cap / chunk), nreq): CTA (x, r) serves entries [x*chunk, (x+1)*chunk) of
+// requester r's queue; CTAs beyond the queue's fill level exit at once
+template<class U>
+__global__ void __launch_bounds__(kGxServeThreads) gx_serve_kernel(gx_owner_t<U> ow) {
+    const int r  = blockIdx.y;
+    unsigned cnt = __ldcg(ow.counter[r]);
+    if (cnt > ow.cap[r]) cnt = ow.cap[r];
+    const unsigned base = blockIdx.x * unsigned(kGxServeChunk);
+    if (base >= cnt) return;
+    const unsigned* __restrict__ queue = ow.queue[r] + base;
+    U* __restrict__ resp               = ow.resp[r] + base;
+    const unsigned left                = cnt - base;
+    unsigned o[kGxServeUnroll];
+    U v[kGxServeUnroll];
 #pragma unroll
-            for (int u = 0; u < UNROLL; ++u) o[u] = __ldcs(queue + i + u * gstride);
-            U v[UNROLL];
+    for (int u = 0; u < kGxServeUnroll; ++u) {
+        const unsigned i = unsigned(u) * kGxServeThreads + threadIdx.x;
+        o[u]             = i < left ? __ldcs(queue + i) : 0u;
+    }
 #pragma unroll
-            for (int u = 0; u < UNROLL; ++u) v[u] = __ldg(ow.src_local + o[u]);
+    for (int u = 0; u < kGxServeUnroll; ++u) v[u] = gx_load_random(ow.src_local + o[u]);
 #pragma unroll
-            for (int u = 0; u < UNROLL; ++u) resp[i + u * gstride] = v[u];
-        }
-        for (; i < cnt; i += gstride) resp[i] = __ldg(ow.src_local + __ldcs(queue + i));
+    for (int u = 0; u < kGxServeUnroll; ++u) {
+        const unsigned i = unsigned(u) * kGxServeThreads + threadIdx.x;
+        if (i < left) resp[i] = v[u];
     }
 }
 
@@ -258,11 +294,11 @@ __global__ void __launch_bounds__(THREADS)
         for (int u = 0; u < UNROLL; ++u) j[u] = (unsigned long long)__ldg(index + i + u * gstride);
         U v[UNROLL];
 #pragma unroll
-        for (int u = 0; u < UNROLL; ++u) v[u] = src[j[u]];
+        for (int u = 0; u < UNROLL; ++u) v[u] = gx_load_random(src + j[u]);
 #pragma unroll
         for (int u = 0; u < UNROLL; ++u) out[i + u * gstride] = v[u];
     }
-    for (; i < n; i += gstride) out[i] = src[(unsigned long long)__ldg(index + i)];
+    for (; i < n; i += gstride) out[i] = gx_load_random(src + (unsigned long long)__ldg(index + i));
 }
 
 }  // namespace sclx::b200

@@ -65,17 +65,17 @@ template<class T>
 void launch_fill(T* out, size_t n, const T& value, const partition_t& p) {
     if (n == 0) return;
     constexpr int V   = vec_traits<T>::width;
-    const size_t work = (n / V + 255) / 256;
+    const size_t work = (n / V + 1023) / 1024;  // one CTA per 256 x 4 vectors, up to kStreamWaves waves
     fill_kernel<T, 256, 4>
-        <<<persistent_grid(work, 8, sm_count_of(p.device)), 256, 0, p.stream>>>(out, n, value);
+        <<<persistent_grid(work, 8, sm_count_of(p.device), kStreamWaves), 256, 0, p.stream>>>(out, n, value);
 }
 
 template<class T>
 void launch_iota(T* out, size_t n, T start, size_t first_index, const partition_t& p) {
     if (n == 0) return;
     constexpr int V   = vec_traits<T>::width;
-    const size_t work = (n / V + 255) / 256;
-    iota_kernel<T, 256, 4><<<persistent_grid(work, 8, sm_count_of(p.device)), 256, 0, p.stream>>>(
+    const size_t work = (n / V + 1023) / 1024;
+    iota_kernel<T, 256, 4><<<persistent_grid(work, 8, sm_count_of(p.device), kStreamWaves), 256, 0, p.stream>>>(
         out, n, start, first_index
     );
 }
@@ -105,7 +105,8 @@ template<class T, class Op>
 void launch_reduce_last_dim(
     const T* in, size_t rows, size_t cols, T identity, T* out, Op op, const partition_t& p
 ) {
-    constexpr int THREADS = 256, UNROLL = 8;
+    // geometry: profiles/r01_rld_tune.txt (16 loads in flight, 2 accumulator sets, 4 CTAs/SM)
+    constexpr int THREADS = 256, UNROLL = 16, ACCS = 2;
     constexpr int V       = vec_traits<T>::width;
     if (rows == 0) return;
     const bool vec_ok  = (rows % V == 0) && is_aligned16(in);
@@ -134,12 +135,12 @@ void launch_reduce_last_dim(
     dim3 grid(grid_x, grid_y);
     if constexpr (V > 1) {
         if (vec_ok) {
-            reduce_last_dim_kernel<T, Op, THREADS, UNROLL, V>
+            reduce_last_dim_kernel<T, Op, THREADS, UNROLL, V, ACCS>
                 <<<grid, THREADS, smem, p.stream>>>(in, rows, cols, identity, out, ws, op);
             return;
         }
     }
-    reduce_last_dim_kernel<T, Op, THREADS, UNROLL, 1>
+    reduce_last_dim_kernel<T, Op, THREADS, UNROLL, 1, ACCS>
         <<<grid, THREADS, smem, p.stream>>>(in, rows, cols, identity, out, ws, op);
 }
 
@@ -226,7 +227,7 @@ void launch_generate(R* out, size_t n, size_t first, Gen gen, const partition_t&
     constexpr int THREADS = 256, UNROLL = 8;
     const size_t work = (n + size_t(THREADS) * UNROLL - 1) / (size_t(THREADS) * UNROLL);
     generate_kernel<R, Gen, THREADS, UNROLL>
-        <<<persistent_grid(work, 8, sm_count_of(p.device)), THREADS, 0, p.stream>>>(
+        <<<persistent_grid(work, 8, sm_count_of(p.device), kStreamWaves), THREADS, 0, p.stream>>>(
             out, n, first, gen
         );
 }

@@ -2,10 +2,9 @@
 //
 // The reference launches ceil(n/block) CTAs per device, capped by the user's grid_size and
 // traits::kernel::max_thread_count (/root/reference scalix/detail/execute_kernel.cuh:137-145).
-// Here the default grid is "as many CTAs as can be resident" (occupancy x SM count, a
-// multiple of the 148 SMs): the kernel's grid-stride loop covers the rest, which removes
-// millions of CTA launches for 2^30-element ranges while keeping every warp's accesses
-// coalesced.  An explicit grid_size from the user is honoured exactly like the reference.
+// Here the default grid is 64 resident waves (occupancy x SM count x 64, a multiple of the
+// 148 SMs): the kernel's grid-stride loop covers the rest, which removes millions of CTA
+// launches for 2^30-element ranges while keeping every warp's accesses coalesced.  An explicit grid_size from the user is honoured exactly like the reference.
 #pragma once
 
 #include <cuda_runtime.h>
@@ -13,6 +12,8 @@
 #include <limits>
 
 namespace sclx::b200 {
+
+constexpr size_t kOversubscribe = 64;
 
 inline int device_sm_count() {
     // per-device cache; the ordinal count of a node is small
@@ -47,7 +48,13 @@ inline cudaError_t range_launch_grid(
             &per_sm, kernel, int(block_threads), dynamic_smem);
         if (e != cudaSuccess) return e;
         if (per_sm < 1) per_sm = 1;
-        const size_t resident = size_t(per_sm) * size_t(device_sm_count());
+        // kOversubscribe resident waves, not one: the loop still strides by the whole grid
+        // (coalesced on every trip), but CTAs of later waves start staggered, which
+        // de-synchronises the load / store phases of the machine.  Measured on B200 with
+        // 2^30-element ranges: axpy lambda 4747 -> 4942 GB/s, random-gather lambda
+        // 38.4 -> 45-48 G loads/s; one CTA per 256 elements (the reference's geometry, 4 M CTAs)
+        // drops to 3930 GB/s (profiles/r01_dispatch_tune.txt, profiles/r01_serve_tune.txt).
+        const size_t resident = size_t(per_sm) * size_t(device_sm_count()) * kOversubscribe;
         if (blocks > resident) blocks = resident;
     }
     if (max_thread_count != std::numeric_limits<size_t>::max()) {

@@ -6,6 +6,7 @@
 // /root/reference scalix/algorithm/inclusive_scan.cuh:48,87-93), and ordered
 // combines so non-commutative operators keep the reference's operand order.
 #pragma once
+#include <cstdlib>
 
 #include <cstddef>
 #include <cstdint>
@@ -162,10 +163,27 @@ combine_left(bool has_left, const T& left, const T& x, Op& op) {
     return has_left ? op(left, x) : x;
 }
 
-// grid sizing: a multiple of the SM count, capped by the work available
+// Grid sizing: `waves` resident waves of ctas_per_sm CTAs per SM (a multiple of the SM count),
+// capped by the work available.  One wave (a truly persistent grid) is NOT the fastest shape
+// for the streaming kernels on B200: CTAs of later waves start staggered and de-synchronise the
+// machine's load and store phases — fill 6037 -> 7518 GB/s, a copy-like generate 5157 -> 6955
+// GB/s, axpy lambda 4747 -> 4942 GB/s from 1 to 64-256 waves (profiles/r01_fill_tune.txt,
+// r01_dispatch_tune.txt).  SCLX_B200_WAVES overrides every kernel's default (tuning only).
+// write-dominated streaming kernels (fill, iota, generate): effectively one CTA per chunk
+constexpr unsigned kStreamWaves = 256;
+
+__host__ inline unsigned tuning_waves(unsigned dflt) {
+    static const int forced = [] {
+        const char* e = std::getenv("SCLX_B200_WAVES");
+        return e ? std::atoi(e) : 0;
+    }();
+    return forced > 0 ? unsigned(forced) : dflt;
+}
+
 __host__ inline unsigned
-persistent_grid(size_t work_items, unsigned ctas_per_sm, int sm_count = kSmCount) {
-    size_t cap = size_t(sm_count) * ctas_per_sm;
+persistent_grid(size_t work_items, unsigned ctas_per_sm, int sm_count = kSmCount, unsigned waves = 1) {
+    size_t cap = size_t(sm_count) * ctas_per_sm * tuning_waves(waves);
+    if (cap > 0x7fffffffull) cap = 0x7fffffffull;
     if (work_items < 1) work_items = 1;
     return unsigned(work_items < cap ? work_items : cap);
 }

@@ -131,7 +131,10 @@ __global__ void __launch_bounds__(THREADS) reduce_kernel(
 //                      VW accumulators live in registers; consecutive threads read
 //                      consecutive vectors (fully coalesced).
 //   slots  > THREADS : blockIdx.y selects a band of THREADS slots.
-template<class T, class Op, int THREADS, int UNROLL, int VW>
+// UNROLL independent vector loads are in flight per thread; they fold into ACCS accumulator
+// sets (ACCS < UNROLL frees registers for more resident CTAs: the loads carry the latency, the
+// adds do not).
+template<class T, class Op, int THREADS, int UNROLL, int VW, int ACCS = UNROLL>
 __global__ void __launch_bounds__(THREADS) reduce_last_dim_kernel(
     const T* __restrict__ in,
     size_t rows,
@@ -163,9 +166,10 @@ __global__ void __launch_bounds__(THREADS) reduce_last_dim_kernel(
     const int slot   = int(tid % band_slots);
     const int group  = int(tid / band_slots);
 
-    T acc[UNROLL][VW];
+    static_assert(ACCS >= 1 && ACCS <= UNROLL && (ACCS & (ACCS - 1)) == 0, "ACCS: power of two <= UNROLL");
+    T acc[ACCS][VW];
 #pragma unroll
-    for (int u = 0; u < UNROLL; ++u)
+    for (int u = 0; u < ACCS; ++u)
 #pragma unroll
         for (int e = 0; e < VW; ++e) acc[u][e] = identity;
 
@@ -182,14 +186,14 @@ __global__ void __launch_bounds__(THREADS) reduce_last_dim_kernel(
 #pragma unroll
                 for (int u = 0; u < UNROLL; ++u)
 #pragma unroll
-                    for (int e = 0; e < VW; ++e) acc[u][e] = op(acc[u][e], v[u].v[e]);
+                    for (int e = 0; e < VW; ++e) acc[u % ACCS][e] = op(acc[u % ACCS][e], v[u].v[e]);
             } else {
                 T v[UNROLL];
 #pragma unroll
                 for (int u = 0; u < UNROLL; ++u)
                     v[u] = __ldg(base + (c + u * col_step) * rows);
 #pragma unroll
-                for (int u = 0; u < UNROLL; ++u) acc[u][0] = op(acc[u][0], v[u]);
+                for (int u = 0; u < UNROLL; ++u) acc[u % ACCS][0] = op(acc[u % ACCS][0], v[u]);
             }
         }
         for (; c < cols; c += col_step) {
@@ -198,9 +202,9 @@ __global__ void __launch_bounds__(THREADS) reduce_last_dim_kernel(
         }
         // pairwise fold of the unrolled accumulators
 #pragma unroll
-        for (int w = 1; w < UNROLL; w <<= 1)
+        for (int w = 1; w < ACCS; w <<= 1)
 #pragma unroll
-            for (int u = 0; u + w < UNROLL; u += 2 * w)
+            for (int u = 0; u + w < ACCS; u += 2 * w)
 #pragma unroll
                 for (int e = 0; e < VW; ++e) acc[u][e] = op(acc[u][e], acc[u + w][e]);
 #pragma unroll
@@ -227,20 +231,54 @@ __global__ void __launch_bounds__(THREADS) reduce_last_dim_kernel(
     if (!s_last) return;
     __threadfence();
 
-    // last CTA: out[r] = identity (+) partial[0][r] (+) partial[1][r] ...
-    // pairwise over 4 interleaved chains to shorten the float dependency chain
-    for (size_t r = tid; r < rows; r += THREADS) {
-        T a0 = identity, a1 = identity, a2 = identity, a3 = identity;
-        unsigned b = 0;
-        for (; b + 3 < gridDim.x; b += 4) {
-            a0 = op(a0, load_cg(partials + size_t(b) * rows + r));
-            a1 = op(a1, load_cg(partials + size_t(b + 1) * rows + r));
-            a2 = op(a2, load_cg(partials + size_t(b + 2) * rows + r));
-            a3 = op(a3, load_cg(partials + size_t(b + 3) * rows + r));
+    // last CTA: out[r] = identity (+) partial[0][r] (+) partial[1][r] ... in a FIXED order.
+    // All threads take part: with rows <= THREADS the CTA range is split into THREADS/rows
+    // contiguous pieces folded side by side (8 independent chains each, so ~8 L2 loads are in
+    // flight per thread), then the pieces are folded in order.  (One thread per row walking
+    // every CTA's partial cost ~45 us of a 670 us kernel at 592 CTAs.)
+    const unsigned nblk = gridDim.x;
+    if (rows <= size_t(THREADS)) {
+        const unsigned pieces = unsigned(THREADS / rows);
+        const unsigned chunk  = (nblk + pieces - 1) / pieces;
+        __syncthreads();
+        if (size_t(tid) < size_t(pieces) * rows) {
+            const size_t r       = size_t(tid) % rows;
+            const unsigned piece = unsigned(size_t(tid) / rows);
+            unsigned b           = piece * chunk;
+            const unsigned end   = b + chunk < nblk ? b + chunk : nblk;
+            T a[8];
+#pragma unroll
+            for (int k = 0; k < 8; ++k) a[k] = identity;
+            for (; b + 7 < end; b += 8) {
+                T v[8];
+#pragma unroll
+                for (int k = 0; k < 8; ++k) v[k] = load_cg(partials + size_t(b + k) * rows + r);
+#pragma unroll
+                for (int k = 0; k < 8; ++k) a[k] = op(a[k], v[k]);
+            }
+            for (; b < end; ++b) a[0] = op(a[0], load_cg(partials + size_t(b) * rows + r));
+            s_acc[size_t(piece) * rows + r]
+                = op(op(op(a[0], a[1]), op(a[2], a[3])), op(op(a[4], a[5]), op(a[6], a[7])));
         }
-        for (; b < gridDim.x; ++b)
-            a0 = op(a0, load_cg(partials + size_t(b) * rows + r));
-        out[r] = op(op(a0, a1), op(a2, a3));
+        __syncthreads();
+        if (size_t(tid) < rows) {
+            T a = s_acc[tid];
+            for (unsigned q = 1; q < pieces; ++q) a = op(a, s_acc[size_t(q) * rows + tid]);
+            out[tid] = a;
+        }
+    } else {
+        for (size_t r = tid; r < rows; r += THREADS) {
+            T a0 = identity, a1 = identity, a2 = identity, a3 = identity;
+            unsigned b = 0;
+            for (; b + 3 < nblk; b += 4) {
+                a0 = op(a0, load_cg(partials + size_t(b) * rows + r));
+                a1 = op(a1, load_cg(partials + size_t(b + 1) * rows + r));
+                a2 = op(a2, load_cg(partials + size_t(b + 2) * rows + r));
+                a3 = op(a3, load_cg(partials + size_t(b + 3) * rows + r));
+            }
+            for (; b < nblk; ++b) a0 = op(a0, load_cg(partials + size_t(b) * rows + r));
+            out[r] = op(op(a0, a1), op(a2, a3));
+        }
     }
     if (tid == 0) *ws.ticket = 0;
 }

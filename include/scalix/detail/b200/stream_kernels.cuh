@@ -101,8 +101,25 @@ struct gather_parts_t {
     int nparts;                         // 1: plain pointer in part[0]
 };
 
+// one random element load with the L2::64B prefetch-size hint: the default fetches 126 B of
+// DRAM per 4-byte random load, the hint 63 B (profiles/r01_fetch_granularity.txt)
+template<class T>
+__device__ __forceinline__ T load_random(const T* p) {
+    if constexpr (sizeof(T) == 4) {
+        unsigned v;
+        asm volatile("ld.global.nc.L2::64B.b32 %0, [%1];" : "=r"(v) : "l"(p));
+        return __builtin_bit_cast(T, v);
+    } else if constexpr (sizeof(T) == 8) {
+        unsigned long long v;
+        asm volatile("ld.global.nc.L2::64B.b64 %0, [%1];" : "=l"(v) : "l"(p));
+        return __builtin_bit_cast(T, v);
+    } else {
+        return __ldg(p);
+    }
+}
+
 // out[i] = src[idx[i]].  Each thread keeps UNROLL independent random loads in
-// flight; index reads are 128-bit coalesced.
+// flight; index reads are coalesced.
 template<class T, class I, int THREADS, int UNROLL>
 __global__ void __launch_bounds__(THREADS) gather_kernel(
     const I* __restrict__ idx,
@@ -121,12 +138,12 @@ __global__ void __launch_bounds__(THREADS) gather_kernel(
 #pragma unroll
         for (int u = 0; u < UNROLL; ++u) {
             if (src.nparts == 1) {
-                v[u] = __ldg(static_cast<const T*>(src.part[0]) + j[u]);
+                v[u] = load_random(static_cast<const T*>(src.part[0]) + j[u]);
             } else {
                 const unsigned long long e = (unsigned long long)j[u];
                 const unsigned long long p = e / src.elems_per_part;
                 const unsigned long long o = e - p * src.elems_per_part;
-                v[u] = __ldg(static_cast<const T*>(src.part[p]) + o);
+                v[u] = load_random(static_cast<const T*>(src.part[p]) + o);
             }
         }
 #pragma unroll

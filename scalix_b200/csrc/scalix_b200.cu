@@ -298,8 +298,10 @@ int launch_reduce(const T* in, size_t n, T identity, T* out, cudaStream_t stream
     return mark_use(*st, stream);
 }
 
+// geometry: profiles/r01_rld_tune.txt (16 loads in flight, 2 accumulator sets, 4 CTAs/SM)
 constexpr int kRldThreads = 256;
-constexpr int kRldUnroll  = 8;
+constexpr int kRldUnroll  = 16;
+constexpr int kRldAccs    = 2;
 
 template<class T, class Op>
 int launch_reduce_last_dim(const T* in, size_t rows, size_t cols, T identity, T* out,
@@ -335,10 +337,10 @@ int launch_reduce_last_dim(const T* in, size_t rows, size_t cols, T identity, T*
     const size_t smem = size_t(kRldThreads) * vw * sizeof(T);
     dim3 grid(grid_x, grid_y);
     if (vec_ok && V > 1)
-        reduce_last_dim_kernel<T, Op, kRldThreads, kRldUnroll, V>
+        reduce_last_dim_kernel<T, Op, kRldThreads, kRldUnroll, V, kRldAccs>
             <<<grid, kRldThreads, smem, stream>>>(in, rows, cols, identity, out, ws, op);
     else
-        reduce_last_dim_kernel<T, Op, kRldThreads, kRldUnroll, 1>
+        reduce_last_dim_kernel<T, Op, kRldThreads, kRldUnroll, 1, kRldAccs>
             <<<grid, kRldThreads, smem, stream>>>(in, rows, cols, identity, out, ws, op);
     SCLX_LAUNCHED();
     return mark_use(*st, stream);
@@ -350,8 +352,8 @@ int launch_fill(T* out, size_t n, T value, cudaStream_t stream) {
     device_state* st = nullptr;
     if (int rc = current_state(&st)) return rc;
     constexpr int V   = vec_traits<T>::width;
-    const size_t work = (n / V + 255) / 256;
-    const unsigned grid = persistent_grid(work, 8, st->sm_count);
+    const size_t work = (n / V + 1023) / 1024;
+    const unsigned grid = persistent_grid(work, 8, st->sm_count, kStreamWaves);
     fill_kernel<T, 256, 4><<<grid, 256, 0, stream>>>(out, n, value);
     SCLX_LAUNCHED();
     return 0;
@@ -363,8 +365,8 @@ int launch_iota(T* out, size_t n, T start, size_t first_index, cudaStream_t stre
     device_state* st = nullptr;
     if (int rc = current_state(&st)) return rc;
     constexpr int V   = vec_traits<T>::width;
-    const size_t work = (n / V + 255) / 256;
-    const unsigned grid = persistent_grid(work, 8, st->sm_count);
+    const size_t work = (n / V + 1023) / 1024;
+    const unsigned grid = persistent_grid(work, 8, st->sm_count, kStreamWaves);
     iota_kernel<T, 256, 4><<<grid, 256, 0, stream>>>(out, n, start, first_index);
     SCLX_LAUNCHED();
     return 0;
@@ -376,9 +378,13 @@ int launch_gather(const I* idx, size_t n, const gather_parts_t& parts, T* out,
     if (n == 0) return 0;
     device_state* st = nullptr;
     if (int rc = current_state(&st)) return rc;
-    const size_t work   = (n + 255) / 256;
-    const unsigned grid = persistent_grid(work, 8, st->sm_count);
-    gather_kernel<T, I, 256, 8><<<grid, 256, 0, stream>>>(idx, n, parts, out);
+    // NOT a persistent grid: a random-access kernel runs ~30 % faster when many small CTAs (one
+    // 1024-index chunk each) start staggered than when one resident wave sweeps in lock step
+    // (experiments/serve_tune.cu, profiles/r01_serve_tune.txt)
+    (void)st;
+    const size_t work   = (n + 1023) / 1024;
+    const unsigned grid = unsigned(work < 0x7fffffffull ? work : 0x7fffffffull);
+    gather_kernel<T, I, 256, 4><<<grid, 256, 0, stream>>>(idx, n, parts, out);
     SCLX_LAUNCHED();
     return 0;
 }
