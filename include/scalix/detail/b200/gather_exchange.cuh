@@ -285,20 +285,27 @@ __global__ void __launch_bounds__(kGxThreads) gx_place_kernel(gx_requester_t<U> 
 template<class U, class I, int THREADS, int UNROLL>
 __global__ void __launch_bounds__(THREADS)
     gather_direct_kernel(const I* __restrict__ index, size_t n, const U* __restrict__ src, U* __restrict__ out) {
-    const size_t gtid    = size_t(blockIdx.x) * THREADS + threadIdx.x;
-    const size_t gstride = size_t(gridDim.x) * THREADS;
-    size_t i             = gtid;
-    for (; i + (UNROLL - 1) * gstride < n; i += UNROLL * gstride) {
+    constexpr size_t CHUNK = size_t(THREADS) * UNROLL;  // contiguous per CTA and trip
+    for (size_t base = size_t(blockIdx.x) * CHUNK; base < n; base += size_t(gridDim.x) * CHUNK) {
+        const size_t left = n - base;
         unsigned long long j[UNROLL];
-#pragma unroll
-        for (int u = 0; u < UNROLL; ++u) j[u] = (unsigned long long)__ldg(index + i + u * gstride);
         U v[UNROLL];
 #pragma unroll
-        for (int u = 0; u < UNROLL; ++u) v[u] = gx_load_random(src + j[u]);
+        for (int u = 0; u < UNROLL; ++u) {
+            const size_t i = size_t(u) * THREADS + threadIdx.x;
+            j[u]           = i < left ? (unsigned long long)__ldg(index + base + i) : 0ull;
+        }
 #pragma unroll
-        for (int u = 0; u < UNROLL; ++u) out[i + u * gstride] = v[u];
+        for (int u = 0; u < UNROLL; ++u) {
+            const size_t i = size_t(u) * THREADS + threadIdx.x;
+            if (i < left) v[u] = gx_load_random(src + j[u]);
+        }
+#pragma unroll
+        for (int u = 0; u < UNROLL; ++u) {
+            const size_t i = size_t(u) * THREADS + threadIdx.x;
+            if (i < left) out[base + i] = v[u];
+        }
     }
-    for (; i < n; i += gstride) out[i] = gx_load_random(src + (unsigned long long)__ldg(index + i));
 }
 
 }  // namespace sclx::b200

@@ -127,36 +127,35 @@ __global__ void __launch_bounds__(THREADS) gather_kernel(
     gather_parts_t src,
     T* __restrict__ out
 ) {
-    const size_t gtid    = size_t(blockIdx.x) * THREADS + threadIdx.x;
-    const size_t gstride = size_t(gridDim.x) * THREADS;
-    size_t i             = gtid;
-    for (; i + (UNROLL - 1) * gstride < n; i += UNROLL * gstride) {
-        I j[UNROLL];
-#pragma unroll
-        for (int u = 0; u < UNROLL; ++u) j[u] = __ldg(idx + i + u * gstride);
+    // a CTA owns one CONTIGUOUS chunk of THREADS*UNROLL indices per trip (launched as one chunk
+    // per CTA): index reads and result writes of a CTA stay in one DRAM page neighbourhood
+    constexpr size_t CHUNK = size_t(THREADS) * UNROLL;
+    for (size_t base = size_t(blockIdx.x) * CHUNK; base < n; base += size_t(gridDim.x) * CHUNK) {
+        const size_t left = n - base;
+        unsigned long long j[UNROLL];
         T v[UNROLL];
 #pragma unroll
         for (int u = 0; u < UNROLL; ++u) {
-            if (src.nparts == 1) {
-                v[u] = load_random(static_cast<const T*>(src.part[0]) + j[u]);
-            } else {
-                const unsigned long long e = (unsigned long long)j[u];
-                const unsigned long long p = e / src.elems_per_part;
-                const unsigned long long o = e - p * src.elems_per_part;
-                v[u] = load_random(static_cast<const T*>(src.part[p]) + o);
+            const size_t i = size_t(u) * THREADS + threadIdx.x;
+            j[u]           = i < left ? (unsigned long long)__ldg(idx + base + i) : 0ull;
+        }
+#pragma unroll
+        for (int u = 0; u < UNROLL; ++u) {
+            const size_t i = size_t(u) * THREADS + threadIdx.x;
+            if (i < left) {
+                if (src.nparts == 1) {
+                    v[u] = load_random(static_cast<const T*>(src.part[0]) + j[u]);
+                } else {
+                    const unsigned long long p = j[u] / src.elems_per_part;
+                    const unsigned long long o = j[u] - p * src.elems_per_part;
+                    v[u] = load_random(static_cast<const T*>(src.part[p]) + o);
+                }
             }
         }
 #pragma unroll
-        for (int u = 0; u < UNROLL; ++u) out[i + u * gstride] = v[u];
-    }
-    for (; i < n; i += gstride) {
-        const unsigned long long e = (unsigned long long)__ldg(idx + i);
-        if (src.nparts == 1) {
-            out[i] = __ldg(static_cast<const T*>(src.part[0]) + e);
-        } else {
-            const unsigned long long p = e / src.elems_per_part;
-            const unsigned long long o = e - p * src.elems_per_part;
-            out[i] = __ldg(static_cast<const T*>(src.part[p]) + o);
+        for (int u = 0; u < UNROLL; ++u) {
+            const size_t i = size_t(u) * THREADS + threadIdx.x;
+            if (i < left) out[base + i] = v[u];
         }
     }
 }
