@@ -330,17 +330,20 @@ def run_ours(args):
     barrier()
 
     # ---- value: K steps, device time, max over ranks ------------------------------------------
-    with ClockSampler(local_rank) as clocks:
-        barrier()
-        l_before = sclx.launch_count()
-        total_ms = time_events(torch, step, args.steps)
-        barrier()
-        gpu_launches = sclx.launch_count() - l_before
-        # dominant kernel alone: one event pair per launch
-        kt = []
-        for _ in range(args.steps):
-            kt.append(time_events(torch, kernel_only, 1))
-        torch.cuda.synchronize()
+    # the sampler stays on through both timed regions (value and e2e): K device-resident
+    # steps last ~12 ms, too short for more than one nvidia-smi sample on their own
+    clocks = ClockSampler(local_rank)
+    clocks.__enter__()
+    barrier()
+    l_before = sclx.launch_count()
+    total_ms = time_events(torch, step, args.steps)
+    barrier()
+    gpu_launches = sclx.launch_count() - l_before
+    # dominant kernel alone: one event pair per launch
+    kt = []
+    for _ in range(args.steps):
+        kt.append(time_events(torch, kernel_only, 1))
+    torch.cuda.synchronize()
     t = torch.tensor([total_ms], dtype=torch.float64, device="cuda")
     if world > 1:
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
@@ -377,6 +380,7 @@ def run_ours(args):
         e2e_step()
     torch.cuda.synchronize()
     e2e_s = time.perf_counter() - t0
+    clocks.__exit__()
     t = torch.tensor([e2e_s], dtype=torch.float64, device="cuda")
     if world > 1:
         dist.all_reduce(t, op=dist.ReduceOp.MAX)

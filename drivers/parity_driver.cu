@@ -9,10 +9,11 @@
 //   parity_driver dump  <case> <n> <outfile>          run a parity case, dump raw result bytes
 //   parity_driver bench <case> <n> <steps> <warmup>   print {"ms_per_step": ..} (wall clock
 //                                                      around the blocking public API call)
-// cases: scan_i32 scan_i64 rld_f32 rld_u32max axpy_f32 axpy_f32_r3 gather_f32 fill_iota serialize gather_x_f32 gather_x_f64 gather_x_skew
+// cases: scan_i32 scan_i64 rld_f32 rld_u32max axpy_f32 axpy_f32_r3 gather_f32 fill_iota serialize gather_x_f32 gather_x_f64 gather_x_skew errors
 #include <scalix/algorithm/inclusive_scan.cuh>
 #include <scalix/algorithm/reduce.cuh>
 #include <scalix/algorithm/reduce_last_dim.cuh>
+#include <scalix/assign_array.cuh>
 #include <scalix/fill.cuh>
 #include <scalix/iota.cuh>
 #include <scalix/scalix.cuh>
@@ -36,6 +37,7 @@
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
+#include <stdexcept>
 #include <string>
 #include <vector>
 
@@ -298,6 +300,71 @@ int run_case(const std::string& what, const std::string& name, size_t n, const c
         return do_dump ? dump(r, path) : bench(step, steps, warmup);
     }
 #endif
+    if (name == "errors") {
+        // error behaviour of the API: which exception class each misuse raises.
+        // One int per probe: 0 = no throw, 1 = std::invalid_argument, 2 = std::runtime_error,
+        // 3 = any other std::exception.  `n` is the size of the arrays involved.
+        auto probe = [](auto&& body) -> int {
+            try {
+                body();
+            } catch (const std::invalid_argument&) {
+                return 1;
+            } catch (const std::runtime_error&) {
+                return 2;
+            } catch (const std::exception&) {
+                return 3;
+            }
+            return 0;
+        };
+        std::vector<int> codes;
+        // shape initialiser list of the wrong length (scalix/shape.cuh:66-69)
+        codes.push_back(probe([&] { sclx::shape_t<2> s{1, 2, 3}; (void)s; }));
+        // inclusive_scan into a result of another shape (scalix/algorithm/inclusive_scan.cuh:52-55)
+        codes.push_back(probe([&] {
+            sclx::array<int, 1> a({n}), r({n + 1});
+            sclx::algorithm::inclusive_scan(a, r, 0, sclx::algorithm::plus<>());
+        }));
+        // reduce_last_dim into a result of the wrong shape (scalix/algorithm/reduce_last_dim.cuh:171-174)
+        codes.push_back(probe([&] {
+            sclx::array<uint, 2> a({3, n});
+            sclx::array<uint, 1> r({4});
+            sclx::algorithm::reduce_last_dim(a, r, 0u, sclx::algorithm::plus<>());
+        }));
+        // assign_array between arrays of different sizes (scalix/assign_array.cuh:42-45)
+        codes.push_back(probe([&] {
+            sclx::array<int, 1> a({n}), b({n / 2});
+            sclx::assign_array(a, b).get();
+        }));
+        // re-partitioning a slice (scalix/array.cuh:525-529)
+        codes.push_back(probe([&] {
+            sclx::array<int, 2> a({4, n});
+            auto row = a.get_slice(sclx::md_index_t<1>{{1}});
+            row.set_primary_devices(std::vector<int>{0});
+        }));
+        // device id beyond the device count (scalix/array.cuh:491-499)
+        codes.push_back(probe([&] {
+            sclx::array<int, 1> a({n});
+            a.set_primary_devices(std::vector<int>{0, 4096});
+        }));
+        // an exception raised inside the host lambda reaches the caller through future::get()
+        // (scalix/execute_kernel.cuh:506-513)
+        codes.push_back(probe([&] {
+            sclx::execute_kernel([&](sclx::kernel_handler&) { throw std::runtime_error("from the host lambda"); }).get();
+        }));
+        // control: well-formed calls do not throw, and the runtime still works afterwards
+        codes.push_back(probe([&] {
+            sclx::array<int, 1> a({n}), r({n});
+            sclx::fill(a, 1);
+            sclx::algorithm::inclusive_scan(a, r, 0, sclx::algorithm::plus<>());
+            if (r[n - 1] != int(n)) throw std::logic_error("scan after the error probes is wrong");
+        }));
+        if (!do_dump) return 2;
+        FILE* f = std::fopen(path, "wb");
+        if (!f) return 3;
+        std::fwrite(codes.data(), sizeof(int), codes.size(), f);
+        std::fclose(f);
+        return 0;
+    }
     std::fprintf(stderr, "unknown case %s\n", name.c_str());
     return 2;
 }
