@@ -34,6 +34,8 @@ CASES = {  # name -> (n, dtype, float tolerance or None)
     "gather_x_f32": (300_007, np.float32, None),
     "gather_x_f64": (150_001, np.float64, None),
     "gather_x_skew": (300_007, np.float32, None),
+    # exception class per API misuse (SURVEY 8b "Errors"): 1 invalid_argument, 2 runtime_error, 0 none
+    "errors": (1000, np.int32, None),
 }
 
 
@@ -82,6 +84,11 @@ def oracle_expected(oracle, case, n):
     if case == "serialize":
         v = np.array([oracle.lib.oracle_splitmix64(0x5E7, i) & 0xFFFFFFFF for i in range(n)], dtype=np.uint64)
         return (v + np.uint64(1)).astype(np.uint32).view(np.int32)
+    if case == "errors":
+        # shape list, scan shape, reduce_last_dim shape -> invalid_argument; assign_array size,
+        # slice re-partition -> runtime_error; device id -> invalid_argument; host-lambda throw
+        # through future::get() -> runtime_error; well-formed control -> no throw
+        return np.array([1, 1, 1, 2, 2, 1, 2, 0], dtype=np.int32)
     if case == "fill_iota":
         return (41 + 1 + np.arange(n, dtype=np.int64)).astype(np.int32)
     return None
