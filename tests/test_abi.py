@@ -88,3 +88,26 @@ def test_product_never_imports_the_oracle():
                 if f.endswith((".py", ".cu", ".cuh", ".h", ".hpp", ".cpp")):
                     text = open(os.path.join(dirpath, f), errors="replace").read()
                     assert "liboracle" not in text and "import oracle" not in text, os.path.join(dirpath, f)
+
+
+def test_cmake_project_defines_the_reference_target(tmp_path):
+    """the `scalix` CMake target of the reference (/root/reference CMakeLists.txt:13-44) exists
+    here under the same name with the same switches, links the runtime library and is
+    B200-only; configure only (no compilation)"""
+    import shutil
+    import subprocess
+
+    text = open(os.path.join(REPO, "CMakeLists.txt")).read()
+    assert "add_library(scalix INTERFACE)" in text
+    for needle in ("--extended-lambda", "--expt-relaxed-constexpr", "SCALIX_DEBUG_KERNEL_LAUNCH",
+                   "SCALIX_EMULATE_MULTIDEVICE", "set(CMAKE_CUDA_ARCHITECTURES 100a)",
+                   "target_link_libraries(scalix INTERFACE scalix_b200)"):
+        assert needle in text, needle
+    cmake = shutil.which("cmake")
+    if cmake is None or shutil.which("nvcc") is None:
+        pytest.skip("cmake or nvcc not on PATH")
+    gen = ["-G", "Ninja"] if shutil.which("ninja") else []
+    p = subprocess.run([cmake, "-S", REPO, "-B", str(tmp_path / "b"), *gen, "-DSCALIX_EMULATE_MULTIDEVICE=4",
+                        "-DSCALIX_DEBUG_KERNEL_LAUNCH=ON"], capture_output=True, text=True, timeout=300)
+    assert p.returncode == 0, p.stdout[-2000:] + p.stderr[-2000:]
+    assert "SCALIX_EMULATE_MULTIDEVICE is set to 4" in p.stdout
