@@ -389,6 +389,14 @@ def run_ours(args):
     if not np.all(np.abs(host_out.astype(np.float64) - want) <= 1e-5 * np.abs(want)) and world == 1:
         raise SystemExit("bench: e2e result outside the 1e-5 tolerance")
 
+    # the bound of the host-buffer path: one plain pinned -> device copy of the same 4 GiB
+    def h2d_copy():
+        sclx.check(sclx.lib.sclx_b200_memcpy_h2d(d_in.ptr, pinned.ptr, nbytes, stream))
+
+    h2d_copy()
+    torch.cuda.synchronize()
+    h2d_peak = nbytes / (time_events(torch, h2d_copy, 2) / 2 * 1e-3) / 1e9
+
     line = None
     if rank == 0:
         line = {
@@ -406,7 +414,9 @@ def run_ours(args):
                          "kernel": "reduce_last_dim_kernel<float, op_plus, 256, 16, 4, 2>",
                          "kernel_ms": round(kernel_ms, 4)},
             "e2e": {"value": round(e2e_value, 2), "unit": UNIT, "h2d_bytes_per_step": nbytes,
-                    "d2h_bytes_per_step": ROWS * 4, "ms_per_step": round(e2e_s / e2e_steps * 1e3, 3)},
+                    "d2h_bytes_per_step": ROWS * 4, "ms_per_step": round(e2e_s / e2e_steps * 1e3, 3),
+                    "bound": "pcie h2d", "h2d_copy_gbs_per_gpu": round(h2d_peak, 2),
+                    "frac_of_h2d_copy": round(e2e_value / world / h2d_peak, 4)},
             "gpu_launches": int(gpu_launches),
             "clocks": clocks.summary(),
         }

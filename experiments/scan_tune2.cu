@@ -11,6 +11,7 @@
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
+#include <algorithm>
 #include <vector>
 using namespace sclx::b200;
 #define CK(x) do { cudaError_t err__ = (x); if (err__ != cudaSuccess) { printf("FAIL %s: %s\n", #x, cudaGetErrorString(err__)); exit(2); } } while (0)
@@ -30,16 +31,18 @@ __global__ void diff_kernel(const T* a, const T* b, size_t n, unsigned long long
 }
 
 static int g_sms = 148;
+static void* g_flush = nullptr;  // FLUSH=1: L2 eviction buffer
 
-template<class T, int VECS, int CHUNKS, int STAGES, int WR, int WS, int LBK, int WLB>
+template<class T, int VECS, int CHUNKS, int STAGES, int WR, int WS, int LBK, int WLB, int RUN = 1>
 void run_stream(const T* in, T* out, const T* want, size_t n, void* desc, unsigned& epoch, scan_stream_counters* ctr,
                 unsigned long long* bad, int reps, const char* sel, int force_cps) {
     char name[64];
-    snprintf(name, sizeof name, "v%dc%ds%d/r%dw%dk%dl%d", VECS, CHUNKS, STAGES, WR, WS, LBK, WLB);
+    if (RUN == 1) snprintf(name, sizeof name, "v%dc%ds%d/r%dw%dk%dl%d", VECS, CHUNKS, STAGES, WR, WS, LBK, WLB);
+    else snprintf(name, sizeof name, "v%dc%ds%d/r%dw%dk%dl%dR%d", VECS, CHUNKS, STAGES, WR, WS, LBK, WLB, RUN);
     if (sel && strcmp(sel, name)) return;
     using cfg = scan_stream_config<T, VECS, CHUNKS, STAGES, WR, WS, WLB>;
     constexpr int THREADS = cfg::threads;
-    auto kern = inclusive_scan_stream_kernel<T, plus_op, VECS, CHUNKS, STAGES, WR, WS, LBK, WLB>;
+    auto kern = inclusive_scan_stream_kernel<T, plus_op, VECS, CHUNKS, STAGES, WR, WS, LBK, WLB, RUN>;
     if (cfg::smem_bytes > 227 * 1024) return;
     CK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, int(cfg::smem_bytes)));
     int occ = 0;
@@ -66,6 +69,18 @@ void run_stream(const T* in, T* out, const T* want, size_t n, void* desc, unsign
     for (int i = 0; i < reps; ++i) launch();
     cudaEventRecord(e); CK((cudaEventSynchronize(e)));
     float ms; cudaEventElapsedTime(&ms, s, e); ms /= reps;
+    if (g_flush) {
+        // config-1 style timing: evict in/out from the 126 MB L2 before every launch, time each
+        // launch on its own, report the median
+        std::vector<float> t;
+        for (int i = 0; i < reps; ++i) {
+            CK(cudaMemsetAsync(g_flush, i, size_t(256) << 20));
+            cudaEventRecord(s); launch(); cudaEventRecord(e); CK(cudaEventSynchronize(e));
+            float one; cudaEventElapsedTime(&one, s, e); t.push_back(one);
+        }
+        std::sort(t.begin(), t.end());
+        ms = t[t.size() / 2];
+    }
     cudaFuncAttributes fa; cudaFuncGetAttributes(&fa, kern);
 #ifdef STATS
     {
@@ -122,6 +137,50 @@ void sweep(size_t n, const char* sel, int reps, int cps) {
         cudaFree(tmp);
     }
 #define R(VE, CH, ST, WR, WS, K, L) run_stream<T, VE, CH, ST, WR, WS, K, L>(in, out, want, n, desc, epoch, ctr, bad, reps, sel, cps)
+#ifdef SWEEP2
+    // second sweep: LB_K = 1 on the geometries that were only tried with LB_K = 2, fewer / more
+    // reducer and scanner warps around the two production points
+    R(5, 16, 5, 8, 16, 1, 1); R(9, 8, 6, 8, 16, 1, 1); R(9, 8, 6, 8, 16, 2, 1); R(5, 14, 6, 8, 16, 1, 1); R(3, 24, 6, 8, 16, 1, 1);
+    R(7, 12, 5, 8, 16, 1, 1); R(7, 10, 6, 8, 16, 1, 1); R(9, 8, 6, 4, 16, 1, 1); R(9, 8, 6, 8, 8, 1, 1); R(5, 16, 5, 4, 16, 1, 1);
+    R(5, 16, 5, 8, 8, 1, 1); R(5, 16, 5, 16, 8, 1, 1); R(11, 6, 6, 6, 12, 1, 1); R(13, 5, 6, 5, 10, 1, 1); R(5, 12, 7, 8, 12, 1, 1);
+    return;
+#endif
+#ifdef SWEEP4
+    // config 1 (2^24 int32, FLUSH=1): does a smaller tile / deeper ring fill and drain faster?
+    R(9, 8, 6, 4, 16, 1, 1); R(5, 16, 5, 8, 16, 1, 1); R(9, 4, 12, 4, 16, 1, 1); R(5, 8, 10, 4, 16, 1, 1); R(9, 6, 8, 4, 16, 1, 1);
+    R(5, 4, 20, 4, 8, 1, 1); R(9, 2, 24, 2, 8, 1, 1); R(9, 8, 6, 8, 16, 1, 1); R(9, 8, 6, 4, 8, 1, 1); R(3, 8, 16, 4, 16, 1, 1);
+    R(9, 3, 16, 3, 12, 1, 1); R(5, 6, 14, 6, 12, 1, 1);
+    return;
+#endif
+#define RR(VE, CH, ST, WR, WS, K, L, RN) run_stream<T, VE, CH, ST, WR, WS, K, L, RN>(in, out, want, n, desc, epoch, ctr, bad, reps, sel, cps)
+#ifdef SWEEP7
+    // runs, taken only when RUN stages are free
+    R(9, 8, 6, 4, 16, 1, 1); RR(9, 8, 6, 4, 16, 1, 1, 2); RR(9, 6, 8, 4, 16, 1, 1, 2); RR(9, 4, 12, 4, 16, 1, 1, 2);
+    RR(9, 4, 12, 4, 16, 1, 1, 3); RR(9, 4, 12, 4, 16, 1, 1, 4); RR(9, 3, 16, 3, 12, 1, 1, 4); RR(5, 8, 10, 4, 16, 1, 1, 2);
+    RR(9, 6, 8, 4, 16, 1, 1, 4); RR(9, 2, 24, 2, 8, 1, 1, 4); RR(9, 2, 24, 2, 8, 1, 1, 8); RR(9, 4, 12, 4, 8, 1, 1, 2);
+    return;
+#endif
+#ifdef SWEEP6
+    // runs of consecutive tiles per ticket: one look-back per run
+    R(9, 8, 6, 4, 16, 1, 1); RR(9, 8, 6, 4, 16, 1, 1, 2); RR(9, 8, 6, 4, 16, 1, 1, 3); RR(9, 8, 6, 4, 16, 1, 1, 6);
+    RR(9, 6, 8, 4, 16, 1, 1, 2); RR(9, 6, 8, 4, 16, 1, 1, 4); RR(9, 4, 12, 4, 16, 1, 1, 4); RR(5, 8, 10, 4, 16, 1, 1, 4);
+    RR(9, 8, 6, 4, 16, 2, 1, 2); RR(9, 8, 6, 8, 16, 1, 1, 2); RR(9, 8, 6, 4, 12, 1, 1, 2); RR(9, 7, 7, 4, 16, 1, 1, 2);
+    return;
+#endif
+#ifdef SWEEP5
+    // look-back window width vs problem size: at start-up no tile carries a PREFIX yet, so the
+    // prefix wavefront advances 32*LB_K tiles per L2 round trip
+    R(9, 8, 6, 4, 16, 1, 1); R(9, 8, 6, 4, 16, 2, 1); R(9, 8, 6, 4, 16, 4, 1); R(9, 8, 6, 4, 16, 8, 1);
+    return;
+#endif
+#ifdef SWEEP3
+    // third sweep: around the sweep-2 winner v9c8s6/r4w16k1
+    R(9, 8, 6, 4, 16, 1, 1); R(9, 8, 6, 2, 16, 1, 1); R(9, 8, 6, 3, 16, 1, 1); R(9, 8, 6, 4, 12, 1, 1); R(9, 8, 6, 4, 20, 1, 1);
+    R(9, 8, 6, 4, 8, 1, 1); R(9, 8, 6, 2, 8, 1, 1); R(9, 8, 6, 4, 16, 1, 2); R(7, 10, 6, 4, 16, 1, 1); R(3, 24, 6, 4, 16, 1, 1);
+    R(9, 6, 8, 4, 16, 1, 1); R(9, 10, 4, 4, 16, 1, 1); R(9, 12, 4, 4, 16, 1, 1); R(11, 7, 5, 4, 16, 1, 1); R(9, 9, 5, 4, 16, 1, 1);
+    R(9, 7, 7, 4, 16, 1, 1); R(5, 14, 6, 4, 16, 1, 1); R(9, 8, 6, 4, 24, 1, 1);
+    return;
+#endif
     R(5, 16, 5, 8, 16, 1, 1); R(5, 16, 5, 8, 16, 2, 1); R(5, 16, 5, 8, 16, 3, 1); R(5, 16, 5, 8, 20, 2, 1); R(5, 16, 5, 6, 12, 2, 1); R(5, 16, 5, 12, 16, 2, 1);
     R(9, 8, 6, 8, 16, 2, 1); R(5, 8, 10, 8, 16, 2, 1); R(5, 12, 7, 8, 12, 2, 1); R(3, 32, 4, 8, 16, 2, 1); R(7, 16, 3, 8, 16, 2, 1); R(7, 12, 5, 8, 16, 2, 1);
     R(5, 20, 4, 8, 16, 2, 1); R(5, 18, 4, 8, 16, 2, 1); R(5, 14, 6, 8, 16, 2, 1); R(3, 24, 6, 8, 16, 2, 1); R(5, 22, 4, 8, 16, 2, 1);
@@ -144,6 +203,7 @@ int main(int argc, char** argv) {
     int cps  = argc > 4 ? atoi(argv[4]) : 0;                                  // cap CTAs/SM
     size_t lg = argc > 5 ? atoi(argv[5]) : 0;
     cudaDeviceGetAttribute(&g_sms, cudaDevAttrMultiProcessorCount, 0);
+    if (getenv("FLUSH")) CK(cudaMalloc(&g_flush, size_t(256) << 20));
     if (!strcmp(ty, "all") || !strcmp(ty, "i32")) sweep<unsigned>(size_t(1) << (lg ? lg : 29), sel, reps, cps);
     if (!strcmp(ty, "all") || !strcmp(ty, "i64")) sweep<unsigned long long>(size_t(1) << (lg ? lg : 28), sel, reps, cps);
     return 0;

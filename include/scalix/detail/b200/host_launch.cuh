@@ -145,10 +145,7 @@ void launch_reduce_last_dim(
 }
 
 // ---- inclusive scan of one partition ---------------------------------------------------------
-// geometry per element width: profiles/r01_scan_stream_sweep.txt
-template<class T>
-constexpr bool is_wide_scan_type = sizeof(T) == 8;
-
+// geometry per element width: scan_stream_geometry (scan_stream.cuh)
 template<class T, class Op>
 void launch_inclusive_scan(
     const T* in, T* out, size_t n, const T* lower_totals, int n_lower, T* total_out, Op op,
@@ -159,12 +156,8 @@ void launch_inclusive_scan(
         "inclusive_scan kernels support trivially copyable element types of 1, 2, 4 or 8 bytes"
     );
     if (n == 0) return;
-    constexpr int VECS   = is_wide_scan_type<T> ? 9 : 5;
-    constexpr int CHUNKS = is_wide_scan_type<T> ? 8 : 16;
-    constexpr int STAGES = is_wide_scan_type<T> ? 6 : 5;
-    constexpr int LB_K   = is_wide_scan_type<T> ? 2 : 1;
-    constexpr int W_RED = 8, W_SCAN = 16;
-    using scfg    = scan_stream_config<T, VECS, CHUNKS, STAGES, W_RED, W_SCAN>;
+    using geo  = scan_stream_geometry<T>;
+    using scfg = typename geo::config;
     using rcfg    = scan_config<T, 256, 6>;
     using desc_io = tile_desc<T>;
 
@@ -182,7 +175,8 @@ void launch_inclusive_scan(
         void* counters = nullptr;
         cuda::detail::check_rt(sclx_b200_rt_scan_counters(p.device, &counters));
         auto kernel
-            = inclusive_scan_stream_kernel<T, Op, VECS, CHUNKS, STAGES, W_RED, W_SCAN, LB_K>;
+            = inclusive_scan_stream_kernel<T, Op, geo::vecs, geo::chunks, geo::stages, geo::w_red,
+                                           geo::w_scan, geo::lb_k>;
         cuda::cuda_exception::raise_if_not_success(
             cudaFuncSetAttribute(
                 kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, int(scfg::smem_bytes)

@@ -213,6 +213,23 @@ struct scan_stream_config {
     static_assert(threads <= 1024, "too many warps");
 };
 
+// Production geometry per element width (profiles/r01_scan_stream_sweep{,2,3}.txt, 2^29
+// elements on a B200): 36 KiB tiles of 8 chunks x 9 vectors per lane in a 6-stage ring
+// (216 KiB), 4 reducer warps, 16 scanner warps, one look-back warp reading 32 descriptors per
+// round trip -> 5941 GB/s for 4-byte and 6322 GB/s for 8-byte elements.  Narrower elements keep
+// 5 vectors per lane so a lane's items (16/sizeof(T) per vector) stay in registers.
+template<class T>
+struct scan_stream_geometry {
+    static constexpr bool wide   = sizeof(T) >= 4;
+    static constexpr int vecs    = wide ? 9 : 5;
+    static constexpr int chunks  = wide ? 8 : 16;
+    static constexpr int stages  = wide ? 6 : 5;
+    static constexpr int w_red   = wide ? 4 : 8;
+    static constexpr int w_scan  = 16;
+    static constexpr int lb_k    = 1;
+    using config = scan_stream_config<T, vecs, chunks, stages, w_red, w_scan>;
+};
+
 struct scan_stream_counters {
     unsigned ticket;  // next tile to hand out
     unsigned exited;  // CTAs that have finished (the last one resets both)
@@ -221,7 +238,7 @@ struct scan_stream_counters {
 // `in`/`out` must be 16-byte aligned (bulk copies); callers fall back to
 // inclusive_scan_kernel<..., ALIGNED=false> otherwise.  `in` may equal `out`.
 template<class T, class Op, int VECS, int CHUNKS, int STAGES, int W_RED, int W_SCAN, int LB_K,
-         int W_LB = 1>
+         int W_LB = 1, int RUN = 1>
 __global__ void __launch_bounds__((2 + W_LB + W_RED + W_SCAN) * 32) inclusive_scan_stream_kernel(
     const T* in,
     T* out,
@@ -237,6 +254,8 @@ __global__ void __launch_bounds__((2 + W_LB + W_RED + W_SCAN) * 32) inclusive_sc
     using desc_io = tile_desc<T>;
     constexpr int V   = cfg::V;
     constexpr int IPT = cfg::items_per_thr;
+    static_assert(RUN >= 1 && (RUN == 1 || W_LB == 1), "runs of tiles need the single look-back warp");
+    static_assert(RUN <= STAGES, "a run must fit in the ring");
 
     extern __shared__ __align__(128) unsigned char s_tiles[];  // STAGES tile buffers
 
@@ -292,13 +311,34 @@ __global__ void __launch_bounds__((2 + W_LB + W_RED + W_SCAN) * 32) inclusive_sc
         // ================= loader ======================================================
         if (lane == 0) {
             int markers = 0;
+            // a ticket is a RUN of consecutive tiles: the look-back warp derives the prefix of
+            // the 2nd..RUNth tile from its own previous tile instead of looking back again.
+            // Measured slower than RUN = 1 on B200 (profiles/r01_scan_stream_sweep{6,7}_*.txt);
+            // production uses 1, the parameter stays for experiments/scan_tune2.cu.
+            size_t run_base = 0;
+            int run_left    = 0;
             for (unsigned it = 0;; ++it) {
                 const int stage      = int(it % STAGES);
                 const unsigned round = it / STAGES;
                 [[maybe_unused]] const long long w0 = SCLX_STAT_CLOCK();
+                if (RUN > 1 && markers == 0 && run_left == 0) {
+                    // take a run only when all of its stages are free (stages recycle in order):
+                    // a ticketed tile whose load has not been issued stalls every later tile's
+                    // look-back
+                    const unsigned last = it + unsigned(RUN) - 1u;
+                    mbar_wait(&s_empty[last % STAGES], ((last / STAGES) & 1u) ^ 1u);
+                }
                 mbar_wait(&s_empty[stage], (round & 1u) ^ 1u);  // fresh barrier: passes
                 SCLX_STAT_ADD(5, SCLX_STAT_CLOCK() - w0);
-                const size_t t = (markers == 0) ? atomicAdd(&counters->ticket, 1u) : num_tiles;
+                size_t t = num_tiles;
+                if (markers == 0) {
+                    if (run_left == 0) {
+                        run_base = atomicAdd(&counters->ticket, unsigned(RUN));
+                        run_left = RUN;
+                    }
+                    t = run_base + size_t(RUN - run_left);
+                    --run_left;
+                }
                 if (t >= num_tiles) {
                     // end of input: one marker per look-back warp flows through the pipeline
                     s_tile_id[stage] = -1;
@@ -361,6 +401,8 @@ __global__ void __launch_bounds__((2 + W_LB + W_RED + W_SCAN) * 32) inclusive_sc
         }
     } else if (warp < 2 + W_LB) {
         // ================= look-back (warp j takes every W_LB-th tile of this CTA) ======
+        long long prev_tile = -2;  // previous tile of this CTA and its inclusive prefix
+        T prev_inclusive{};
         for (unsigned it = unsigned(warp - 2);; it += W_LB) {
             const int stage      = int(it % STAGES);
             const unsigned round = it / STAGES;
@@ -372,18 +414,23 @@ __global__ void __launch_bounds__((2 + W_LB + W_RED + W_SCAN) * 32) inclusive_sc
             }
             // the aggregate (tile 0: the prefix) was already published by the reducers
             if (lane == 0) SCLX_STAT_SINCE(10, stage);
+            const T own_total = s_chunk_incl[stage][CHUNKS - 1];
             T tile_prefix{};
             if (tile > 0) {
                 [[maybe_unused]] const long long c0 = SCLX_STAT_CLOCK();
-                tile_prefix
-                    = lookback_prefix<T, Op, LB_K>(desc, tile, st_aggregate, st_prefix, lane, op);
+                if (RUN > 1 && tile == prev_tile + 1)
+                    tile_prefix = prev_inclusive;  // same run: the predecessor was ours
+                else
+                    tile_prefix = lookback_prefix<T, Op, LB_K>(desc, tile, st_aggregate, st_prefix,
+                                                               lane, op);
                 if (lane == 0) {
                     SCLX_STAT_ADD(0, SCLX_STAT_CLOCK() - c0);
                     SCLX_STAT_ADD(7, 1);
-                    desc_io::store(desc + tile, st_prefix,
-                                   op(tile_prefix, s_chunk_incl[stage][CHUNKS - 1]));
+                    desc_io::store(desc + tile, st_prefix, op(tile_prefix, own_total));
                 }
             }
+            prev_tile      = tile;
+            prev_inclusive = tile > 0 ? op(tile_prefix, own_total) : own_total;
             const T cex = s_chunk_incl[stage][(lane > 0 && lane < CHUNKS) ? lane - 1 : 0];
             if (lane < CHUNKS)
                 s_chunk_prefix[stage][lane]

@@ -203,30 +203,17 @@ T load_scalar(const void* p) {
 }
 
 // ---- launch helpers -----------------------------------------------------------------
-// Scan geometry (profiles/r01_scan_stream_sweep.txt): the streaming kernel for 16-byte
+// Scan geometry (scan_stream_geometry, scan_stream.cuh): the streaming kernel for 16-byte
 // aligned slices, the register look-back kernel for unaligned ones.
 constexpr int kScanThreads = 256;  // register kernel
 constexpr int kScanVecs    = 6;
-
-template<class T>
-struct stream_geometry {  // 4-byte (and narrower) elements
-    static constexpr int vecs = 5, chunks = 16, stages = 5, w_red = 8, w_scan = 16, lb_k = 1;
-};
-template<>
-struct stream_geometry<u64_t> {
-    static constexpr int vecs = 9, chunks = 8, stages = 6, w_red = 8, w_scan = 16, lb_k = 2;
-};
-template<>
-struct stream_geometry<i64_t> : stream_geometry<u64_t> {};
-template<>
-struct stream_geometry<double> : stream_geometry<u64_t> {};
 
 template<class T, class Op>
 int launch_scan(const T* in, T* out, size_t n, const T* lower, int n_lower, T* total_out,
                 cudaStream_t stream, Op op) {
     using desc_io = tile_desc<T>;
-    using geo     = stream_geometry<T>;
-    using scfg    = scan_stream_config<T, geo::vecs, geo::chunks, geo::stages, geo::w_red, geo::w_scan>;
+    using geo     = scan_stream_geometry<T>;
+    using scfg    = typename geo::config;
     using rcfg    = scan_config<T, kScanThreads, kScanVecs>;
     if (n == 0) return 0;
     device_state* st = nullptr;
