@@ -23,10 +23,33 @@
 
 #include <iostream>
 #include <mutex>
+#include <string>
 #include <tuple>
+#include <typeinfo>
 #include <vector>
 
+// -DSCALIX_NVTX: one NVTX range per launch group, named after the kernel tag, so a timeline
+// (Nsight Systems / ncu --nvtx) shows which sclx launch a kernel belongs to.  Header-only
+// NVTX v3 from the CUDA toolkit; a no-op unless a profiler is attached.
+#ifdef SCALIX_NVTX
+#include <nvtx3/nvToolsExt.h>
+#endif
+
 namespace sclx::detail {
+
+struct nvtx_range {
+#ifdef SCALIX_NVTX
+    explicit nvtx_range(const char* what, const char* tag) {
+        std::string name = std::string(what) + " [" + tag + "]";
+        nvtxRangePushA(name.c_str());
+    }
+    ~nvtx_range() { nvtxRangePop(); }
+#else
+    explicit nvtx_range(const char*, const char*) {}
+#endif
+    nvtx_range(const nvtx_range&)            = delete;
+    nvtx_range& operator=(const nvtx_range&) = delete;
+};
 
 #ifdef SCALIX_DEBUG_KERNEL_LAUNCH
 constexpr bool _debug_kernel_launch = true;
@@ -131,6 +154,7 @@ struct tag_executor {
         using functor_t = std::decay_t<F>;
         auto kernel     = Kernels::template range<functor_t, RangeRank, ThreadBlockRank>();
         const unsigned block_threads = unsigned(block_shape.elements());
+        nvtx_range trace("sclx range launch", typeid(Kernels).name());
         std::unique_lock<std::mutex> debug_lock(_debug_kernel_mutex::get(), std::defer_lock);
         if constexpr (_debug_kernel_launch) {
             debug_lock.lock();
@@ -188,6 +212,7 @@ struct tag_executor {
         constexpr uint range_rank = generator_t::range_rank;
         auto kernel = Kernels::template generator<functor_t, generator_t, ThreadBlockRank>();
         const unsigned block_threads = unsigned(block_shape.elements());
+        nvtx_range trace("sclx index-generator launch", typeid(Kernels).name());
         std::unique_lock<std::mutex> debug_lock(_debug_kernel_mutex::get(), std::defer_lock);
         if constexpr (_debug_kernel_launch) {
             debug_lock.lock();
