@@ -9,10 +9,14 @@
 //   parity_driver dump  <case> <n> <outfile>          run a parity case, dump raw result bytes
 //   parity_driver bench <case> <n> <steps> <warmup>   print {"ms_per_step": ..} (wall clock
 //                                                      around the blocking public API call)
-// cases: scan_i32 scan_i64 rld_f32 rld_u32max axpy_f32 axpy_f32_r3 gather_f32 fill_iota serialize gather_x_f32 gather_x_f64 gather_x_skew errors
+// cases: scan_i32 scan_i64 rld_f32 rld_u32max axpy_f32 axpy_f32_r3 gather_f32 fill_iota serialize gather_x_f32 gather_x_f64 gather_x_skew errors algos
+#include <scalix/algorithm/count_if.cuh>
+#include <scalix/algorithm/elementwise_reduce.cuh>
+#include <scalix/algorithm/extrema.cuh>
 #include <scalix/algorithm/inclusive_scan.cuh>
 #include <scalix/algorithm/reduce.cuh>
 #include <scalix/algorithm/reduce_last_dim.cuh>
+#include <scalix/algorithm/transform.cuh>
 #include <scalix/assign_array.cuh>
 #include <scalix/fill.cuh>
 #include <scalix/iota.cuh>
@@ -54,6 +58,10 @@ __host__ __device__ inline float uniform01(unsigned long long seed, unsigned lon
 __host__ __device__ inline float symmetric(unsigned long long seed, unsigned long long i) {
     return uniform01(seed, i) * 2.0f - 1.0f;
 }
+
+struct is_even {
+    __host__ __device__ bool operator()(const int& v) const { return (v & 1) == 0; }
+};
 
 template<class T, uint Rank, class Gen>
 void generate(sclx::array<T, Rank>& arr, Gen gen) {
@@ -300,6 +308,46 @@ int run_case(const std::string& what, const std::string& name, size_t n, const c
         return do_dump ? dump(r, path) : bench(step, steps, warmup);
     }
 #endif
+    if (name == "algos") {
+        // the thin algorithm/ entry points: transform, elementwise_reduce,
+        // assign_array (int -> float), count_if, min_element, max_element, reduce.
+        // Output: n values t[i] + e[i] + int(f[i]), then count, min, max, sum(t).
+        sclx::array<int, 1> a({n}), b({n}), c({n}), t({n}), e({n});
+        sclx::array<float, 1> f({n});
+        generate(a, [] __device__(size_t i) { return int(splitmix64(0xA1, i) & 0xFFFF); });
+        generate(b, [] __device__(size_t i) { return int(splitmix64(0xB2, i) & 0xFF); });
+        generate(c, [] __device__(size_t i) { return int(splitmix64(0xC3, i) & 0xF); });
+        sclx::algorithm::transform(t, a, 3, sclx::algorithm::multiplies<>()).get();
+        sclx::algorithm::elementwise_reduce(sclx::algorithm::plus<>(), e, a, b, c).get();
+        sclx::assign_array(a, f).get();
+        const size_t evens = sclx::algorithm::count_if(a, is_even{});
+        const int lo       = sclx::algorithm::min_element(a);
+        const int hi       = sclx::algorithm::max_element(a);
+        const int total    = sclx::algorithm::reduce(t, 0, sclx::algorithm::plus<>());
+        sclx::array<int, 1> r({n});
+        sclx::execute_kernel([&](sclx::kernel_handler& handler) {
+            handler.launch(
+                sclx::md_range_t<1>{r.shape()},
+                r,
+                [=] __device__(const sclx::md_index_t<1>& idx, const auto&) {
+                    r[idx] = t[idx] + e[idx] + int(f[idx]);
+                }
+            );
+        }).get();
+        if (!do_dump) return 2;
+        std::vector<int> host(n + 4);
+        cudaDeviceSynchronize();
+        if (cudaMemcpy(host.data(), r.data().get(), sizeof(int) * n, cudaMemcpyDefault) != cudaSuccess) return 3;
+        host[n]     = int(evens);
+        host[n + 1] = lo;
+        host[n + 2] = hi;
+        host[n + 3] = total;
+        FILE* out = std::fopen(path, "wb");
+        if (!out) return 4;
+        std::fwrite(host.data(), sizeof(int), host.size(), out);
+        std::fclose(out);
+        return 0;
+    }
     if (name == "errors") {
         // error behaviour of the API: which exception class each misuse raises.
         // One int per probe: 0 = no throw, 1 = std::invalid_argument, 2 = std::runtime_error,

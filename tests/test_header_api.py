@@ -36,6 +36,8 @@ CASES = {  # name -> (n, dtype, float tolerance or None)
     "gather_x_skew": (300_007, np.float32, None),
     # exception class per API misuse (SURVEY 8b "Errors"): 1 invalid_argument, 2 runtime_error, 0 none
     "errors": (1000, np.int32, None),
+    # transform, elementwise_reduce, assign_array, count_if, min/max_element, reduce
+    "algos": (10_007, np.int32, None),
 }
 
 
@@ -84,6 +86,14 @@ def oracle_expected(oracle, case, n):
     if case == "serialize":
         v = np.array([oracle.lib.oracle_splitmix64(0x5E7, i) & 0xFFFFFFFF for i in range(n)], dtype=np.uint64)
         return (v + np.uint64(1)).astype(np.uint32).view(np.int32)
+    if case == "algos":
+        a = oracle.masked_i64(n, 0xA1, 0xFFFF)
+        b = oracle.masked_i64(n, 0xB2, 0xFF)
+        c = oracle.masked_i64(n, 0xC3, 0xF)
+        # t = 3a, e = a + b + c, f = float(a) (exact below 2^24): r = t + e + int(f)
+        tail = [int(np.count_nonzero(a % 2 == 0)), int(a.min()), int(a.max()), int((3 * a).sum())]
+        assert tail[3] < 2**31
+        return np.concatenate([5 * a + b + c, np.array(tail, dtype=np.int64)]).astype(np.int32)
     if case == "errors":
         # shape list, scan shape, reduce_last_dim shape -> invalid_argument; assign_array size,
         # slice re-partition -> runtime_error; device id -> invalid_argument; host-lambda throw
