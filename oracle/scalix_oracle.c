@@ -13,7 +13,11 @@
  * asserted nowhere in the reference ("parity unpinned" there); for those the oracle is an
  * fp64 sum and the tolerance is BASELINE.json's 1e-5 relative.  On the GPU box the tests
  * additionally diff against the reference's own UM build (oracle/_ref, built by
- * oracle/Makefile from the sources where they lie under /root/reference).
+ * oracle/Makefile from the sources where they lie under /root/reference).  Outputs of that
+ * build for small instances of every driver case (run on a B200 by
+ * tests/golden/make_reference_golden.sh) are committed under tests/golden/ref/ and
+ * tests/test_oracle.py checks this file against them on the CPU: bit-exact for integer work
+ * and data movement, 1e-5 relative for the float row sums.
  *
  * The arithmetic the reference delegates to Thrust/CUB (CUDA toolkit, un-vendored; the
  * reference pins only CUDAToolkit >= 12.0, CMakeLists.txt:11; this image: CUDA 12.9 =

@@ -143,3 +143,30 @@ def test_hostloop_baselines_agree_with_oracle(oracle):
     oracle.lib.hostloop_inclusive_scan_plus(x.ctypes.data_as(C.c_void_p), y.ctypes.data_as(C.c_void_p),
                                             x.size, 4, 4)
     assert np.array_equal(y, np.cumsum(x, dtype=np.uint32))
+
+
+def _reference_goldens():
+    import glob
+    import os
+
+    here = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", "ref")
+    out = []
+    for path in sorted(glob.glob(os.path.join(here, "*.bin"))):
+        case, n = os.path.basename(path)[:-4].rsplit("_", 1)
+        out.append((case, int(n), path))
+    return out
+
+
+@pytest.mark.parametrize("case,n,path", _reference_goldens(), ids=lambda v: str(v) if not str(v).startswith("/") else "")
+def test_oracle_matches_outputs_of_the_reference_build(oracle, case, n, path):
+    """tests/golden/ref/*.bin are outputs of the UNMODIFIED reference (its Unified-Memory build of
+    drivers/parity_driver.cu, run on a B200 by tests/golden/make_reference_golden.sh).  The CPU
+    oracle must reproduce them: bit-exact for integer work and data movement, 1e-5 relative
+    for the float row sums (BASELINE.json's tolerance)."""
+    from test_header_api import CASES, compare, oracle_expected
+
+    _, dtype, tol = CASES[case]
+    want = oracle_expected(oracle, case, n)
+    assert want is not None, case
+    got = np.fromfile(path, dtype=dtype)
+    compare(got, want, tol, f"{case} n={n}: reference build output vs CPU oracle")
