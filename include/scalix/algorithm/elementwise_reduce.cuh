@@ -14,6 +14,7 @@
 
 namespace sclx::algorithm {
 
+// true when all arrays have the same shape (pairwise, left to right)
 template<class T, class U, uint Rank, class... Ts>
 bool check_shapes(
     const sclx::array<T, Rank>& a,
@@ -25,7 +26,11 @@ bool check_shapes(
     return true;
 }
 
-// left fold of op over one index of several arrays
+// left fold of op over one index of several arrays: compute(i, op) = op(...op(op(a[i], b[i]),
+// c[i])..., z[i]), evaluated by compile-time recursion over the pack so that the operand
+// order (and therefore non-commutative or rounding-sensitive ops) matches the reference.
+// Holds raw pointers, not array handles: the functor travels into generate_kernel by value
+// and the arrays themselves are kept alive by the caller until the returned future is ready.
 template<class R, class T, class U, uint Rank, class... Ts>
 struct reduce_along_index {
     const T* a_;

@@ -11,6 +11,10 @@
 
 namespace sclx {
 
+// N handles (not N copies of the data): an sclx::array is a reference-counted view, so the
+// list is N pointers + shapes, cheap to pass by value into a kernel.  Inside a device lambda
+// `list[k][idx]` addresses element idx of the k-th array; on the host the launcher iterates the
+// list to validate last extents and partitioning before it queues anything.
 template<class T, uint Rank, uint N>
 class array_list {
   public:
@@ -20,6 +24,7 @@ class array_list {
     array_list(array_list&&) noexcept            = default;
     array_list& operator=(array_list&&) noexcept = default;
 
+    // array_list<T> -> array_list<const T> (read-only views of the same storage)
     template<class T_ = const T>
     __host__ operator array_list<T_, Rank, N>() const {  // NOLINT
         static_assert(std::is_same_v<T_, const T>, "Can only cast to const");
@@ -27,6 +32,8 @@ class array_list {
         return array_list<T_, Rank, N>(const_arrays);
     }
 
+    // the four ways the reference allows a list to be built: braces, std::vector, raw pointer
+    // to N arrays, std::array; the first two check the count against N (std::invalid_argument)
     __host__ array_list(std::initializer_list<array<T, Rank>> arrays) {
         check_count(arrays.size());
         constexpr_assign_array<N>(arrays_, arrays.begin());
@@ -45,6 +52,7 @@ class array_list {
         constexpr_assign_array<N>(arrays_, arrays.data());
     }
 
+    // k-th array (no bounds check, as in the reference)
     __host__ __device__ array<T, Rank>& operator[](size_t i) { return arrays_[i]; }
     __host__ __device__ const array<T, Rank>& operator[](size_t i) const { return arrays_[i]; }
 

@@ -29,7 +29,19 @@ namespace sclx {
 
 class kernel_handler {
   public:
+    // defaults of every launch overload below (values of sclx::cuda::traits::kernel): 1-D blocks
+    // of 256 threads; "no cap" for the grid, which the dispatcher then sizes to the machine
+    static constexpr uint tb_rank_default = cuda::traits::kernel::default_block_shape.rank();
+    static constexpr shape_t<1> block_default() { return cuda::traits::kernel::default_block_shape; }
+    static constexpr size_t grid_default() { return cuda::traits::kernel::default_grid_size; }
+
     // ---- range launches ---------------------------------------------------------------
+    // launch(range, array_list, f): the general range form (reference :49-72).  All result
+    // arrays must share their last extent (std::invalid_argument otherwise) and are brought to
+    // the first one's partitioning (with the reference's warning) if they differ; partition p
+    // runs the range indices whose last coordinate falls in its slice, on p's device, on that
+    // device's persistent stream.  `block_shape` only shapes local_thread_id();
+    // `grid_size` caps the grid (default: sized to the machine by launch_config.cuh).
     template<
         class KernelTag = detail::default_kernel_tag,
         uint RangeRank,
@@ -37,70 +49,78 @@ class kernel_handler {
         uint ResultRank,
         uint NResult,
         class F,
-        uint ThreadBlockRank = cuda::traits::kernel::default_block_shape.rank()>
+        uint ThreadBlockRank = tb_rank_default>
     __host__ void launch(
         md_range_t<RangeRank> range,
         array_list<T, ResultRank, NResult> result,
         F&& f,
-        shape_t<ThreadBlockRank> block_shape = cuda::traits::kernel::default_block_shape,
-        size_t grid_size                     = cuda::traits::kernel::default_grid_size
+        shape_t<ThreadBlockRank> block_shape = block_default(),
+        size_t grid_size                     = grid_default()
     ) const {
         launch_array_list_impl<KernelTag>(range, result, block_shape, grid_size, std::forward<F>(f));
     }
 
+    // same for a run-time sized list (reference :74-96)
     template<
         class KernelTag = detail::default_kernel_tag,
         uint RangeRank,
         class T,
         uint ResultRank,
         class F,
-        uint ThreadBlockRank = cuda::traits::kernel::default_block_shape.rank()>
+        uint ThreadBlockRank = tb_rank_default>
     __host__ void launch(
         md_range_t<RangeRank> range,
         dynamic_array_list<T, ResultRank> result,
         F&& f,
-        shape_t<ThreadBlockRank> block_shape = cuda::traits::kernel::default_block_shape,
-        size_t grid_size                     = cuda::traits::kernel::default_grid_size
+        shape_t<ThreadBlockRank> block_shape = block_default(),
+        size_t grid_size                     = grid_default()
     ) const {
         launch_array_list_impl<KernelTag>(range, result, block_shape, grid_size, std::forward<F>(f));
     }
 
+    // single result array (reference :98-120): wrapped in a one-element array_list
     template<
         class KernelTag = detail::default_kernel_tag,
         uint RangeRank,
         class T,
         uint ResultRank,
         class F,
-        uint ThreadBlockRank = cuda::traits::kernel::default_block_shape.rank()>
+        uint ThreadBlockRank = tb_rank_default>
     __host__ void launch(
         md_range_t<RangeRank> range,
         array<T, ResultRank> result,
         F&& f,
-        shape_t<ThreadBlockRank> block_shape = cuda::traits::kernel::default_block_shape,
-        size_t grid_size                     = cuda::traits::kernel::default_grid_size
+        shape_t<ThreadBlockRank> block_shape = block_default(),
+        size_t grid_size                     = grid_default()
     ) const {
         launch<KernelTag>(
             range, array_list<T, ResultRank, 1>({result}), std::forward<F>(f), block_shape, grid_size
         );
     }
 
+    // heterogeneous results (reference :195-216): array_tuple of arrays with equal last extents
     template<
         class KernelTag = detail::default_kernel_tag,
         uint RangeRank,
         class F,
-        uint ThreadBlockRank = cuda::traits::kernel::default_block_shape.rank(),
+        uint ThreadBlockRank = tb_rank_default,
         class... ArrayTypes>
     __host__ void launch(
         md_range_t<RangeRank> range,
         array_tuple<ArrayTypes...> result,
         F&& f,
-        shape_t<ThreadBlockRank> block_shape = cuda::traits::kernel::default_block_shape,
-        size_t grid_size                     = cuda::traits::kernel::default_grid_size
+        shape_t<ThreadBlockRank> block_shape = block_default(),
+        size_t grid_size                     = grid_default()
     ) const {
         launch_tuple_impl<KernelTag>(range, result, block_shape, grid_size, std::forward<F>(f));
     }
 
     // ---- index-generator launches -------------------------------------------------------
+    // launch(index_generator, results, f) (reference :122-146): EVERY partition walks the whole
+    // generator range, maps each range index through the generator and calls f only for the
+    // indices whose last coordinate it owns — writes stay local, reads may be anywhere.  The
+    // generator is copied to the device by value; its index_range()'s last extent must equal
+    // the results' last extent.
     template<
         class KernelTag = detail::default_kernel_tag,
         class IndexGenerator,
@@ -108,13 +128,13 @@ class kernel_handler {
         uint ResultRank,
         uint NResult,
         class F,
-        uint ThreadBlockRank = cuda::traits::kernel::default_block_shape.rank()>
+        uint ThreadBlockRank = tb_rank_default>
     __host__ void launch(
         IndexGenerator&& index_generator,
         array_list<T, ResultRank, NResult> result,
         F&& f,
-        shape_t<ThreadBlockRank> block_shape = cuda::traits::kernel::default_block_shape,
-        size_t grid_size                     = cuda::traits::kernel::default_grid_size
+        shape_t<ThreadBlockRank> block_shape = block_default(),
+        size_t grid_size                     = grid_default()
     ) const {
         launch_array_list_impl<KernelTag>(
             std::forward<IndexGenerator>(index_generator), result, block_shape, grid_size,
@@ -122,19 +142,20 @@ class kernel_handler {
         );
     }
 
+    // index generator, run-time sized list (reference :148-170)
     template<
         class KernelTag = detail::default_kernel_tag,
         class IndexGenerator,
         class T,
         uint ResultRank,
         class F,
-        uint ThreadBlockRank = cuda::traits::kernel::default_block_shape.rank()>
+        uint ThreadBlockRank = tb_rank_default>
     __host__ void launch(
         IndexGenerator&& index_generator,
         dynamic_array_list<T, ResultRank> result,
         F&& f,
-        shape_t<ThreadBlockRank> block_shape = cuda::traits::kernel::default_block_shape,
-        size_t grid_size                     = cuda::traits::kernel::default_grid_size
+        shape_t<ThreadBlockRank> block_shape = block_default(),
+        size_t grid_size                     = grid_default()
     ) const {
         launch_array_list_impl<KernelTag>(
             std::forward<IndexGenerator>(index_generator), result, block_shape, grid_size,
@@ -142,19 +163,20 @@ class kernel_handler {
         );
     }
 
+    // index generator, single result array (reference :172-193)
     template<
         class KernelTag = detail::default_kernel_tag,
         class IndexGenerator,
         class T,
         uint ResultRank,
         class F,
-        uint ThreadBlockRank = cuda::traits::kernel::default_block_shape.rank()>
+        uint ThreadBlockRank = tb_rank_default>
     __host__ void launch(
         IndexGenerator&& index_generator,
         array<T, ResultRank> result,
         F&& f,
-        shape_t<ThreadBlockRank> block_shape = cuda::traits::kernel::default_block_shape,
-        size_t grid_size                     = cuda::traits::kernel::default_grid_size
+        shape_t<ThreadBlockRank> block_shape = block_default(),
+        size_t grid_size                     = grid_default()
     ) const {
         launch<KernelTag>(
             std::forward<IndexGenerator>(index_generator),
@@ -165,18 +187,19 @@ class kernel_handler {
         );
     }
 
+    // index generator, heterogeneous results (reference :218-239)
     template<
         class KernelTag = detail::default_kernel_tag,
         class IndexGenerator,
         class F,
-        uint ThreadBlockRank = cuda::traits::kernel::default_block_shape.rank(),
+        uint ThreadBlockRank = tb_rank_default,
         class... ArrayTypes>
     __host__ void launch(
         IndexGenerator&& index_generator,
         array_tuple<ArrayTypes...> result,
         F&& f,
-        shape_t<ThreadBlockRank> block_shape = cuda::traits::kernel::default_block_shape,
-        size_t grid_size                     = cuda::traits::kernel::default_grid_size
+        shape_t<ThreadBlockRank> block_shape = block_default(),
+        size_t grid_size                     = grid_default()
     ) const {
         launch_tuple_impl<KernelTag>(
             std::forward<IndexGenerator>(index_generator), result, block_shape, grid_size,
@@ -184,7 +207,9 @@ class kernel_handler {
         );
     }
 
-    // usable inside device lambdas that captured the handler by value
+    // block-level barrier and device-wide memory fence for device lambdas that captured the
+    // handler by value (a lambda filling a local_array cooperatively needs the first one
+    // before any thread reads what its neighbours wrote)
     __device__ void syncthreads() const { __syncthreads(); }
     __device__ void threadfence() const { __threadfence(); }
 
@@ -197,7 +222,10 @@ class kernel_handler {
         return local_mem + offset;
     }
 
-    // every result array must be partitioned like the first one
+    // Every result array must be partitioned like the first one: the launcher issues one
+    // kernel per partition of result[0] and a thread may only write what its device owns.
+    // A differing array is re-partitioned on the spot (its pages move, pointer and contents
+    // stay) and the reference's warning is printed.
     template<class ArrayListType>
     __host__ static auto unify_split(ArrayListType& result) {
         auto device_split_first = get_device_split_info(result[0]);
@@ -331,6 +359,8 @@ class local_array {
   public:
     local_array() = default;
 
+    // host side: reserve elements()*sizeof(T) bytes of the launch's dynamic shared memory,
+    // aligned for T, after whatever earlier local_arrays of the same handler took
     __host__ local_array(kernel_handler& handler, const shape_t<Rank>& shape) : shape_(shape) {
         const size_t misalign = handler.local_mem_size_ % alignof(T);
         if (misalign != 0) handler.local_mem_size_ += alignof(T) - misalign;
@@ -338,6 +368,7 @@ class local_array {
         handler.local_mem_size_ += elements() * sizeof(T);
     }
 
+    // device side: element access, column-major like sclx::array (index 0 fastest)
     __device__ T& operator[](const md_index_t<Rank>& idx) { return data()[idx.as_linear(shape_)]; }
 
     __device__ T& operator[](const index_t& idx) { return data()[idx]; }
@@ -351,6 +382,8 @@ class local_array {
 
     __host__ __device__ const shape_t<Rank>& shape() const { return shape_; }
 
+    // first use inside a kernel turns the host-computed byte offset into a pointer into this
+    // block's dynamic shared memory; the lambda must therefore be `mutable`
     __device__ T* data() {
         if (!data_) data_ = reinterpret_cast<T*>(kernel_handler::get_local_mem(offset_));
         return data_;

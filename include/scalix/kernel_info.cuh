@@ -18,6 +18,9 @@ class kernel_info {
     kernel_info& operator=(const kernel_info&)     = default;
     kernel_info& operator=(kernel_info&&) noexcept = default;
 
+    // built by the launcher once per partition: `device_range` is `global_range` with the
+    // last extent cut to the partition's slice, `start_index` is zero except for the slice's
+    // first column, `device_id` is the partition's ordinal
     __host__ kernel_info(
         const md_range_t<ProblemRank>& global_range,
         const md_range_t<ProblemRank>& device_range,
@@ -32,6 +35,7 @@ class kernel_info {
           start_linear_(start_index.as_linear(global_range)),
           device_id_(device_id) {}
 
+    // ---- what was launched --------------------------------------------------------------
     __host__ __device__ const shape_t<ThreadBlockRank>& thread_block_shape() const {
         return thread_block_shape_;
     }
@@ -45,6 +49,9 @@ class kernel_info {
         return start_index_;
     }
 
+    // ---- who am I -----------------------------------------------------------------------
+    // position inside the thread block, decomposed against thread_block_shape(); the usual
+    // index into a local_array (examples/scaling_performance.cu:66-72)
     __device__ md_index_t<ThreadBlockRank> local_thread_id() const {
         return md_index_t<>::create_from_linear(threadIdx.x, thread_block_shape_);
     }
@@ -67,6 +74,8 @@ class kernel_info {
     // /root/reference scalix/detail/execute_kernel.cuh:147-153
     __host__ __device__ const int& device_id() const { return device_id_; }
 
+    // grid-stride bookkeeping: the dispatcher bumps stride_count() after every trip, so
+    // global_thread_linear_id() keeps naming the element in flight
     __device__ uint grid_stride() const { return gridDim.x * blockDim.x; }
     __device__ const uint& stride_count() const { return stride_count_; }
     __device__ void increment_stride_count() { ++stride_count_; }
