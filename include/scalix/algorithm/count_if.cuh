@@ -36,11 +36,12 @@ __host__ size_t count_if(const array<T, Rank>& arr, F&& f) {
     const auto device_info  = get_device_split_info(arr);
     const int nparts        = int(device_info.size());
     const value_t* in       = arr.data().get();
-    count_t* partials       = b200::scratch<count_t>(size_t(nparts));
+    b200::call_workspaces ws(device_info);  // leased for this call only
+    count_t* partials       = ws.scratch<count_t>(size_t(nparts));
     map_t map{std::decay_t<F>(f)};
     b200::for_each_partition(arr, device_info, [&](const b200::partition_t& p) {
         b200::launch_map_reduce<value_t, count_t, map_t, detail::add_counts>(
-            in + p.offset, p.elements, count_t(0), partials + p.ordinal, map, detail::add_counts{}, p
+            in + p.offset, p.elements, count_t(0), partials + p.ordinal, map, detail::add_counts{}, p, ws
         );
     });
     b200::sync_devices(b200::devices_of(device_info));

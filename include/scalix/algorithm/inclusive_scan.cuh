@@ -79,35 +79,36 @@ __host__ void inclusive_scan(
         const T* in             = arr.data().get();
         T* out                  = result.data().get();
         functor_t op(f);
+        b200::call_workspaces ws(device_info);  // leased for this call only
 
         if (nparts == 1) {
             b200::for_each_partition(arr, device_info, [&](const b200::partition_t& p) {
                 b200::launch_inclusive_scan<T, functor_t>(
-                    in + p.offset, out + p.offset, p.elements, nullptr, 0, nullptr, op, p
+                    in + p.offset, out + p.offset, p.elements, nullptr, 0, nullptr, op, p, ws
                 );
             });
         } else if constexpr (detail::is_known_commutative_v<functor_t> && std::is_arithmetic_v<T>) {
             // pass A: totals of every partition but the last, into peer-visible scratch
-            T* totals       = b200::scratch<T>(size_t(nparts));
+            T* totals       = ws.scratch<T>(size_t(nparts));
             const T neutral = detail::neutral_element<functor_t, T>();
             b200::for_each_partition(arr, device_info, [&](const b200::partition_t& p) {
                 if (p.ordinal + 1 < nparts)
                     b200::launch_reduce<T, functor_t>(
-                        in + p.offset, p.elements, neutral, totals + p.ordinal, op, p
+                        in + p.offset, p.elements, neutral, totals + p.ordinal, op, p, ws
                     );
             });
             // pass B (ordered after A on every device by the launch-group events)
             b200::for_each_partition(arr, device_info, [&](const b200::partition_t& p) {
                 b200::launch_inclusive_scan<T, functor_t>(
-                    in + p.offset, out + p.offset, p.elements, totals, p.ordinal, nullptr, op, p
+                    in + p.offset, out + p.offset, p.elements, totals, p.ordinal, nullptr, op, p, ws
                 );
             });
         } else {
             // generic functor: the reference's three stages on top of the scan kernel
-            T* lasts = b200::scratch<T>(size_t(nparts));
+            T* lasts = ws.scratch<T>(size_t(nparts));
             b200::for_each_partition(arr, device_info, [&](const b200::partition_t& p) {
                 b200::launch_inclusive_scan<T, functor_t>(
-                    in + p.offset, out + p.offset, p.elements, nullptr, 0, lasts + p.ordinal, op, p
+                    in + p.offset, out + p.offset, p.elements, nullptr, 0, lasts + p.ordinal, op, p, ws
                 );
             });
             const auto devices = b200::devices_of(device_info);

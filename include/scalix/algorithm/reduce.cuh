@@ -21,10 +21,11 @@ __host__ T reduce(const array<T, Rank>& arr, const T& identity, F&& f) {
     const int nparts        = int(device_info.size());
     const value_t* in       = arr.data().get();
     functor_t op(f);
-    value_t* partials = b200::scratch<value_t>(size_t(nparts));
+    b200::call_workspaces ws(device_info);  // leased for this call only
+    value_t* partials = ws.scratch<value_t>(size_t(nparts));
     b200::for_each_partition(arr, device_info, [&](const b200::partition_t& p) {
         b200::launch_reduce<value_t, functor_t>(
-            in + p.offset, p.elements, identity, partials + p.ordinal, op, p
+            in + p.offset, p.elements, identity, partials + p.ordinal, op, p, ws
         );
     });
     b200::sync_devices(b200::devices_of(device_info));

@@ -8,8 +8,9 @@
 //               (ibid. :184-211).
 //   here      : ONE kernel per partition that reads every byte once, coalesced, and produces all
 //               `stride` partial results (reduce_last_dim_kernel); partial rows land in
-//               peer-visible scratch and a tiny kernel folds them in FIXED partition order
-//               (fold_rows_contig_kernel) — float results are bit-stable run to run.
+//               peer-visible scratch (plain NVLink stores) and the partition that finishes LAST
+//               folds them in FIXED partition order inside the same kernel (row_exchange_t) —
+//               one launch group, float results bit-stable run to run.
 // `f` must be associative and commutative (as thrust::reduce requires of the reference's
 // callers) and `identity` neutral for it.
 #pragma once
@@ -81,34 +82,33 @@ __host__ void reduce_last_dim(
 
     if constexpr (std::is_same_v<T, ResultT>) {
         T* out = result.data().get();
+        b200::call_workspaces ws(device_info);  // leased for this call only
         if (nparts == 1) {
             b200::for_each_partition(arr, device_info, [&](const b200::partition_t& p) {
                 b200::launch_reduce_last_dim<T, functor_t>(
-                    in + p.offset, rows, rows ? p.elements / rows : 0, identity, out, op, p
+                    in + p.offset, rows, rows ? p.elements / rows : 0, identity, out, op, p, ws
                 );
             });
             b200::sync_devices(b200::devices_of(device_info));
         } else {
-            T* partial_rows = b200::scratch<T>(size_t(nparts) * rows);
+            // ONE launch group: every partition's kernel stores its row in peer-visible
+            // scratch and the last one to arrive folds all rows in fixed partition order
+            // straight into `result` (row_exchange_t, reduce.cuh) — no second group, no
+            // cross-device event waits, no host fold
+            const size_t row_bytes = (size_t(nparts) * rows * sizeof(T) + 255) / 256 * 256;
+            char* block            = ws.scratch<char>(row_bytes + 256);
+            b200::row_exchange_t xchg;
+            xchg.rows      = block;
+            xchg.arrivals  = reinterpret_cast<unsigned*>(block + row_bytes);
+            xchg.final_out = out;
+            xchg.nparts    = nparts;
             b200::for_each_partition(arr, device_info, [&](const b200::partition_t& p) {
+                b200::row_exchange_t mine = xchg;
+                mine.ordinal              = p.ordinal;
                 b200::launch_reduce_last_dim<T, functor_t>(
-                    in + p.offset, rows, rows ? p.elements / rows : 0, identity,
-                    partial_rows + size_t(p.ordinal) * rows, op, p
+                    in + p.offset, rows, rows ? p.elements / rows : 0, identity, nullptr, op, p, ws, mine
                 );
             });
-            // fixed-order fold on the first partition's device, ordered after all partials
-            const sclx::detail::device_info_t folder{device_info[0]};
-            sclx::detail::run_launch_group(
-                folder,
-                [&](int, int device_id, size_t, size_t, cudaStream_t stream) {
-                    unsigned grid = unsigned((rows + 255) / 256);
-                    const unsigned cap = unsigned(b200::sm_count_of(device_id)) * 8u;
-                    if (grid > cap) grid = cap;
-                    if (grid == 0) return;
-                    b200::fold_rows_contig_kernel<T, functor_t>
-                        <<<grid, 256, 0, stream>>>(partial_rows, nparts, rows, identity, out, op);
-                }
-            );
             auto devices = b200::devices_of(device_info);
             b200::sync_devices(devices);
         }

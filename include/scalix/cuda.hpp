@@ -18,6 +18,7 @@
 #include <cuda_runtime.h>
 
 #include <atomic>
+#include <chrono>
 #include <condition_variable>
 #include <cstdlib>
 #include <deque>
@@ -180,6 +181,9 @@ inline memory_status_info query_memory_status(int device = 0) {
     cudaError_t err = cudaMemGetInfo(&free, &total);
     set_device(before);
     cuda_exception::raise_if_not_success(err, std::experimental::source_location::current());
+    // arrays parked in the runtime's reuse pool are handed back on demand: count them as free
+    free += sclx_b200_rt_pool_bytes_on(device);
+    if (free > total) free = total;
     // emulated devices share one GPU
     int sharing = 0;
     for (int d = 0; d < traits::device_count(); ++d)
@@ -255,8 +259,11 @@ class stream_t {
 namespace detail {
 
 // One persistent host thread per logical device, bound to that device for its whole
-// life.  Workers sleep on a condition variable (the reference's pool spins with
-// yield(), /root/reference scalix/detail/cuda.hpp:70-95).
+// life (the reference's pool spins with yield() forever,
+// /root/reference scalix/detail/cuda.hpp:70-95).  A worker that has just finished a job keeps
+// polling for the next one for a short while before it goes to sleep on its condition
+// variable, so the launch groups of a multi-pass algorithm or of a loop of launches are handed
+// over in well under a microsecond, and an idle process burns no CPU.
 class device_workers {
   public:
     static device_workers& instance() {
@@ -264,6 +271,7 @@ class device_workers {
         return pool;
     }
 
+    // task_scheduler::submit_task: run `f` on the device's thread, result through a future
     template<class F>
     auto submit(int device_id, F&& f) -> std::future<std::invoke_result_t<std::decay_t<F>>> {
         using result_t = std::invoke_result_t<std::decay_t<F>>;
@@ -271,13 +279,36 @@ class device_workers {
             throw_exception<std::invalid_argument>("device id out of range", "sclx::cuda::");
         auto task   = std::make_shared<std::packaged_task<result_t()>>(std::forward<F>(f));
         auto future = task->get_future();
-        worker& w   = *workers_[device_id];
-        {
-            std::lock_guard<std::mutex> lock(w.mutex);
-            w.queue.emplace_back([task] { (*task)(); });
-        }
-        w.wake.notify_one();
+        enqueue(*workers_[device_id], [task] { (*task)(); });
         return future;
+    }
+
+    // fork-join used by launch groups: job(i) runs on the thread of devices[i] for every
+    // i in [0, n); returns when all have finished and rethrows the first exception
+    template<class Job>
+    void run_on(const int* devices, int n, Job&& job) {
+        for (int i = 0; i < n; ++i)
+            if (devices[i] < 0 || devices[i] >= int(workers_.size()))
+                throw_exception<std::invalid_argument>("device id out of range", "sclx::cuda::");
+        struct join_t {
+            std::atomic<int> remaining;
+            std::mutex mutex;
+            std::exception_ptr first;
+        } join{{n}, {}, {}};
+        for (int i = 0; i < n; ++i)
+            enqueue(*workers_[devices[i]], [&join, &job, i] {
+                try {
+                    job(i);
+                } catch (...) {
+                    std::lock_guard<std::mutex> lock(join.mutex);
+                    if (!join.first) join.first = std::current_exception();
+                }
+                join.remaining.fetch_sub(1, std::memory_order_release);
+            });
+        // the jobs only queue kernels (microseconds): poll, then be polite
+        for (unsigned spins = 0; join.remaining.load(std::memory_order_acquire) != 0; ++spins)
+            if (spins > 4096) std::this_thread::yield();
+        if (join.first) std::rethrow_exception(join.first);
     }
 
     ~device_workers() {
@@ -286,6 +317,7 @@ class device_workers {
                 std::lock_guard<std::mutex> lock(w->mutex);
                 w->stop = true;
             }
+            w->pending.fetch_add(1, std::memory_order_release);
             w->wake.notify_one();
         }
         for (auto& w : workers_) w->thread.join();
@@ -296,17 +328,41 @@ class device_workers {
         std::mutex mutex;
         std::condition_variable wake;
         std::deque<std::function<void()>> queue;
+        std::atomic<int> pending{0};  // queued jobs, read by the polling worker without the lock
         bool stop = false;
         std::thread thread;
     };
 
+    static void enqueue(worker& w, std::function<void()> fn) {
+        {
+            std::lock_guard<std::mutex> lock(w.mutex);
+            w.queue.emplace_back(std::move(fn));
+        }
+        w.pending.fetch_add(1, std::memory_order_release);
+        w.wake.notify_one();
+    }
+
+    static long poll_microseconds() {
+        if (const char* e = std::getenv("SCLX_B200_WORKER_SPIN_US")) return std::atol(e);
+        return 200;
+    }
+
     explicit device_workers(int count) {
+        const auto poll = std::chrono::microseconds(poll_microseconds());
         for (int d = 0; d < count; ++d) {
             workers_.emplace_back(new worker);
             worker* w = workers_.back().get();
-            w->thread = std::thread([w, d] {
+            w->thread = std::thread([w, d, poll] {
                 cudaSetDevice(sclx_b200_rt_physical_device(d));
                 for (;;) {
+                    // hot phase: the next job usually follows within microseconds
+                    const auto t0 = std::chrono::steady_clock::now();
+                    while (w->pending.load(std::memory_order_acquire) == 0
+                           && std::chrono::steady_clock::now() - t0 < poll) {
+#if defined(__x86_64__)
+                        __builtin_ia32_pause();
+#endif
+                    }
                     std::function<void()> job;
                     {
                         std::unique_lock<std::mutex> lock(w->mutex);
@@ -315,6 +371,7 @@ class device_workers {
                         job = std::move(w->queue.front());
                         w->queue.pop_front();
                     }
+                    w->pending.fetch_sub(1, std::memory_order_relaxed);
                     job();
                 }
             });

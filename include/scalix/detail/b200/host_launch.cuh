@@ -10,6 +10,7 @@
 #include "scan_stream.cuh"
 #include "stream_kernels.cuh"
 
+#include <exception>
 #include <type_traits>
 #include <vector>
 
@@ -55,6 +56,57 @@ inline void sync_devices(const std::vector<int>& devices) {
     cuda::detail::check_rt(sclx_b200_rt_sync_devices(int(devices.size()), devices.data()));
 }
 
+// Workspace leases of ONE algorithm call: a kernel workspace (partials, tickets, look-back
+// descriptors) per partition's device and any number of small peer-visible scratch blocks.
+// Everything goes back to the runtime's free lists when the call ends, so two calls in
+// flight on different host threads never share a buffer — the reference keeps these
+// function-local (/root/reference scalix/algorithm/reduce_last_dim.cuh:180-211,
+// scalix/algorithm/inclusive_scan.cuh:75-123).
+class call_workspaces {
+  public:
+    explicit call_workspaces(const sclx::detail::device_info_t& device_info) {
+        leases_.reserve(device_info.size());
+        try {
+            for (const auto& part : device_info) {
+                void* lease = nullptr;
+                cuda::detail::check_rt(sclx_b200_rt_workspace_acquire(std::get<0>(part), &lease));
+                leases_.push_back(lease);
+            }
+        } catch (...) {
+            release();
+            throw;
+        }
+    }
+    call_workspaces(const call_workspaces&)            = delete;
+    call_workspaces& operator=(const call_workspaces&) = delete;
+    ~call_workspaces() { release(); }
+
+    // the lease of partition `ordinal`
+    void* lease(int ordinal) const { return leases_[size_t(ordinal)]; }
+
+    // `count` elements of peer-visible scratch (per-partition totals / partial rows)
+    template<class T>
+    T* scratch(size_t count) {
+        void* ptr = nullptr;
+        cuda::detail::check_rt(sclx_b200_rt_scratch_acquire(count * sizeof(T), &ptr));
+        scratch_.push_back(ptr);
+        return static_cast<T*>(ptr);
+    }
+
+  private:
+    void release() {
+        // a call that ends in an exception may leave tickets / arrival counters half-way: the
+        // runtime re-zeroes such blocks before it hands them out again
+        const int poisoned = std::uncaught_exceptions() > 0 ? 1 : 0;
+        for (void* lease : leases_) sclx_b200_rt_workspace_release(lease, poisoned);
+        for (void* ptr : scratch_) sclx_b200_rt_scratch_release(ptr, poisoned);
+        leases_.clear();
+        scratch_.clear();
+    }
+    std::vector<void*> leases_;
+    std::vector<void*> scratch_;
+};
+
 inline int sm_count_of(int logical_device) {
     const int sms = sclx_b200_rt_sm_count(logical_device);
     return sms > 0 ? sms : kSmCount;
@@ -82,15 +134,17 @@ void launch_iota(T* out, size_t n, T start, size_t first_index, const partition_
 
 // ---- whole-partition reduce (op must be associative and commutative) ------------------------
 template<class T, class Op>
-void launch_reduce(const T* in, size_t n, T identity, T* out, Op op, const partition_t& p) {
+void launch_reduce(
+    const T* in, size_t n, T identity, T* out, Op op, const partition_t& p, const call_workspaces& ws_pool
+) {
     constexpr int THREADS = 256, VECS = 8;
     constexpr int V       = vec_traits<T>::width;
     const size_t work     = (n / V + THREADS - 1) / THREADS;
     const unsigned grid   = persistent_grid(work, 8, sm_count_of(p.device));
     void *partials = nullptr, *ticket = nullptr;
-    cuda::detail::check_rt(
-        sclx_b200_rt_reduce_workspace(p.device, size_t(grid) * sizeof(T), &partials, &ticket)
-    );
+    cuda::detail::check_rt(sclx_b200_rt_workspace_reduce(
+        ws_pool.lease(p.ordinal), size_t(grid) * sizeof(T), &partials, &ticket
+    ));
     reduce_workspace_t ws{partials, static_cast<unsigned*>(ticket)};
     if (is_aligned16(in))
         reduce_kernel<T, Op, THREADS, VECS, true>
@@ -103,7 +157,8 @@ void launch_reduce(const T* in, size_t n, T identity, T* out, Op op, const parti
 // ---- reduce along the last dimension for one partition ------------------------------------
 template<class T, class Op>
 void launch_reduce_last_dim(
-    const T* in, size_t rows, size_t cols, T identity, T* out, Op op, const partition_t& p
+    const T* in, size_t rows, size_t cols, T identity, T* out, Op op, const partition_t& p,
+    const call_workspaces& ws_pool, const row_exchange_t& xchg = row_exchange_t{}
 ) {
     // geometry: profiles/r01_rld_tune.txt (16 loads in flight, 2 accumulator sets, 4 CTAs/SM)
     constexpr int THREADS = 256, UNROLL = 16, ACCS = 2;
@@ -127,8 +182,8 @@ void launch_reduce_last_dim(
         if (grid_x > per_band) grid_x = per_band;
     }
     void *partials = nullptr, *ticket = nullptr;
-    cuda::detail::check_rt(sclx_b200_rt_reduce_workspace(
-        p.device, size_t(grid_x) * rows * sizeof(T), &partials, &ticket
+    cuda::detail::check_rt(sclx_b200_rt_workspace_reduce(
+        ws_pool.lease(p.ordinal), size_t(grid_x) * rows * sizeof(T), &partials, &ticket
     ));
     reduce_workspace_t ws{partials, static_cast<unsigned*>(ticket)};
     const size_t smem = size_t(THREADS) * vw * sizeof(T);
@@ -136,12 +191,12 @@ void launch_reduce_last_dim(
     if constexpr (V > 1) {
         if (vec_ok) {
             reduce_last_dim_kernel<T, Op, THREADS, UNROLL, V, ACCS>
-                <<<grid, THREADS, smem, p.stream>>>(in, rows, cols, identity, out, ws, op);
+                <<<grid, THREADS, smem, p.stream>>>(in, rows, cols, identity, out, ws, op, xchg);
             return;
         }
     }
     reduce_last_dim_kernel<T, Op, THREADS, UNROLL, 1, ACCS>
-        <<<grid, THREADS, smem, p.stream>>>(in, rows, cols, identity, out, ws, op);
+        <<<grid, THREADS, smem, p.stream>>>(in, rows, cols, identity, out, ws, op, xchg);
 }
 
 // ---- inclusive scan of one partition ---------------------------------------------------------
@@ -149,7 +204,7 @@ void launch_reduce_last_dim(
 template<class T, class Op>
 void launch_inclusive_scan(
     const T* in, T* out, size_t n, const T* lower_totals, int n_lower, T* total_out, Op op,
-    const partition_t& p
+    const partition_t& p, const call_workspaces& ws_pool
 ) {
     static_assert(
         std::is_trivially_copyable_v<T> && (sizeof(T) <= 4 || sizeof(T) == 8) && (16 % sizeof(T) == 0),
@@ -166,14 +221,14 @@ void launch_inclusive_scan(
     const size_t tiles      = (n + tile_items - 1) / tile_items;
     if (tiles > 0x7fffffffull)
         throw_exception<std::invalid_argument>("partition too large", "sclx::algorithm::");
-    void* desc_raw = nullptr;
+    void *desc_raw = nullptr, *counters = nullptr;
     unsigned epoch = 0;
-    cuda::detail::check_rt(sclx_b200_rt_scan_workspace(p.device, tiles, &desc_raw, &epoch));
+    cuda::detail::check_rt(sclx_b200_rt_workspace_scan(
+        ws_pool.lease(p.ordinal), tiles, int(desc_io::bytes), &desc_raw, &epoch, &counters
+    ));
     auto* desc = static_cast<typename desc_io::word_t*>(desc_raw);
     scan_carry_t carry{lower_totals, n_lower};
     if (aligned) {
-        void* counters = nullptr;
-        cuda::detail::check_rt(sclx_b200_rt_scan_counters(p.device, &counters));
         auto kernel
             = inclusive_scan_stream_kernel<T, Op, geo::vecs, geo::chunks, geo::stages, geo::w_red,
                                            geo::w_scan, geo::lb_k>;
@@ -200,15 +255,16 @@ void launch_inclusive_scan(
 // ---- map-reduce of one partition (count_if, extrema) ------------------------------------------
 template<class T, class R, class Map, class Op>
 void launch_map_reduce(
-    const T* in, size_t n, R identity, R* out, Map map, Op op, const partition_t& p
+    const T* in, size_t n, R identity, R* out, Map map, Op op, const partition_t& p,
+    const call_workspaces& ws_pool
 ) {
     constexpr int THREADS = 256, UNROLL = 8;
     const size_t work   = (n + THREADS - 1) / THREADS;
     const unsigned grid = persistent_grid(work, 8, sm_count_of(p.device));
     void *partials = nullptr, *ticket = nullptr;
-    cuda::detail::check_rt(
-        sclx_b200_rt_reduce_workspace(p.device, size_t(grid) * sizeof(R), &partials, &ticket)
-    );
+    cuda::detail::check_rt(sclx_b200_rt_workspace_reduce(
+        ws_pool.lease(p.ordinal), size_t(grid) * sizeof(R), &partials, &ticket
+    ));
     reduce_workspace_t ws{partials, static_cast<unsigned*>(ticket)};
     map_reduce_kernel<T, R, Map, Op, THREADS, UNROLL>
         <<<grid, THREADS, 0, p.stream>>>(in, n, identity, out, ws, map, op);
@@ -224,14 +280,6 @@ void launch_generate(R* out, size_t n, size_t first, Gen gen, const partition_t&
         <<<persistent_grid(work, 8, sm_count_of(p.device), kStreamWaves), THREADS, 0, p.stream>>>(
             out, n, first, gen
         );
-}
-
-// small peer-visible scratch (per-partition totals / partial rows), valid until the next call
-template<class T>
-T* scratch(size_t count) {
-    void* ptr = nullptr;
-    cuda::detail::check_rt(sclx_b200_rt_scratch(count * sizeof(T), &ptr));
-    return static_cast<T*>(ptr);
 }
 
 }  // namespace sclx::b200

@@ -46,6 +46,21 @@ struct reduce_workspace_t {
     unsigned* ticket;        // zero-initialised, self-resetting
 };
 
+// Cross-partition step of reduce_last_dim fused into the kernel (replaces the mutex-ordered
+// host fold of /root/reference scalix/algorithm/reduce_last_dim.cuh:208-211 AND a second launch
+// group): every partition's kernel stores its row into peer-visible memory `rows`
+// ([nparts][row length], plain NVLink stores), then bumps `arrivals` with a system-scope
+// atomic; the partition that arrives LAST folds all rows in fixed partition order into
+// `final_out`.  Nobody waits for anybody, so it is deadlock-free whatever the devices'
+// relative timing (or when N logical devices share one GPU).  nparts <= 1: no exchange.
+struct row_exchange_t {
+    void* rows         = nullptr;  // [nparts][rows], peer-visible
+    unsigned* arrivals = nullptr;  // zero-initialised, wraps back to zero (atomicInc)
+    void* final_out    = nullptr;  // rows values, peer-visible
+    int nparts         = 0;
+    int ordinal        = 0;
+};
+
 // ---------------------------------------------------------------------------
 // whole-slice reduce
 // ---------------------------------------------------------------------------
@@ -140,9 +155,10 @@ __global__ void __launch_bounds__(THREADS) reduce_last_dim_kernel(
     size_t rows,
     size_t cols,
     T identity,
-    T* __restrict__ out,  // rows values
+    T* __restrict__ out,  // rows values (ignored when xchg.nparts > 1)
     reduce_workspace_t ws,
-    Op op
+    Op op,
+    row_exchange_t xchg = row_exchange_t{}
 ) {
     extern __shared__ __align__(16) unsigned char s_raw[];
     T* s_acc = reinterpret_cast<T*>(s_raw);  // [groups][slots_in_band*VW]
@@ -237,6 +253,8 @@ __global__ void __launch_bounds__(THREADS) reduce_last_dim_kernel(
     // flight per thread), then the pieces are folded in order.  (One thread per row walking
     // every CTA's partial cost ~45 us of a 670 us kernel at 592 CTAs.)
     const unsigned nblk = gridDim.x;
+    const bool exchange = xchg.nparts > 1;
+    if (exchange) out = static_cast<T*>(xchg.rows) + size_t(xchg.ordinal) * rows;
     if (rows <= size_t(THREADS)) {
         const unsigned pieces = unsigned(THREADS / rows);
         const unsigned chunk  = (nblk + pieces - 1) / pieces;
@@ -281,6 +299,23 @@ __global__ void __launch_bounds__(THREADS) reduce_last_dim_kernel(
         }
     }
     if (tid == 0) *ws.ticket = 0;
+    if (!exchange) return;
+
+    // fused cross-partition fold: publish this partition's row, the last arrival folds
+    __threadfence_system();
+    __syncthreads();
+    if (tid == 0)
+        s_last = atomicInc_system(xchg.arrivals, unsigned(xchg.nparts - 1)) == unsigned(xchg.nparts - 1);
+    __syncthreads();
+    if (!s_last) return;
+    __threadfence_system();
+    const T* all = static_cast<const T*>(xchg.rows);
+    T* final_out = static_cast<T*>(xchg.final_out);
+    for (size_t r = tid; r < rows; r += THREADS) {
+        T a = identity;
+        for (int q = 0; q < xchg.nparts; ++q) a = op(a, load_cg(all + size_t(q) * rows + r));
+        final_out[r] = a;
+    }
 }
 
 // out[r] = fold over p (fixed order 0..nparts-1) of parts[p][r], seeded with identity

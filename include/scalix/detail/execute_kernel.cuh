@@ -80,8 +80,11 @@ struct launch_record {
 
 using device_info_t = std::vector<std::tuple<int, size_t, size_t>>;
 
+// launch groups of at most this many devices are queued by the calling thread itself
+constexpr int inline_issue_limit = 2;
+
 // `issue(ordinal, device_id, slice_idx, slice_size, stream)` queues one kernel; called with
-// the device current, inline for one device, on the device's persistent thread otherwise
+// the device current: inline for small groups, on the devices' persistent threads otherwise
 template<class Issue>
 void run_launch_group(const device_info_t& device_info, Issue&& issue) {
     cuda::detail::ensure_runtime();
@@ -100,24 +103,12 @@ void run_launch_group(const device_info_t& device_info, Issue&& issue) {
             cudaGetLastError(), std::experimental::source_location::current(), "sclx::detail::"
         );
     };
-    if (n == 1) {
-        issue_one(0);
+    if (n <= inline_issue_limit) {
+        // one or two kernels are queued faster from here than a hand-over costs
+        for (int i = 0; i < n; ++i) issue_one(i);
     } else {
-        std::vector<std::future<void>> issued;
-        issued.reserve(n);
-        for (int i = 0; i < n; ++i)
-            issued.emplace_back(cuda::detail::device_workers::instance().submit(
-                devices[i], [&issue_one, i] { issue_one(i); }
-            ));
-        std::exception_ptr first;
-        for (auto& fut : issued) {
-            try {
-                fut.get();
-            } catch (...) {
-                if (!first) first = std::current_exception();
-            }
-        }
-        if (first) std::rethrow_exception(first);
+        // one persistent thread per device queues its kernel: N launches in parallel
+        cuda::detail::device_workers::instance().run_on(devices.data(), n, issue_one);
     }
     cuda::set_device(caller_device);
     cuda::detail::check_rt(sclx_b200_rt_end_launch(n, devices.data()));

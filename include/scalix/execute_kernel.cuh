@@ -8,10 +8,9 @@
 //               and blocks until all streams are idle (ibid. :286,300-302,506-513).
 //   here      : the host lambda runs at once on the calling thread and only QUEUES kernels on
 //               the persistent per-device streams; ordering between consecutive launches is
-//               kept on the device with events; the returned std::future<void> synchronises
-//               the streams that were used when it is waited on.  Anything that reads results
-//               on the host (array::operator[] through the mirror, algorithm return values)
-//               synchronises by itself, so a dropped future is harmless.
+//               kept on the device with events.  The returned std::future<void> behaves like
+//               the reference's (never deferred, blocks when dropped while work is running,
+//               delivers errors through get()); see execute_kernel below.
 #pragma once
 
 #include "array.cuh"
@@ -23,6 +22,7 @@
 #include "range.cuh"
 #include "shape.cuh"
 
+#include <chrono>
 #include <future>
 
 namespace sclx {
@@ -399,9 +399,33 @@ class local_array {
     T* data_{};  // resolved on first use inside the kernel
 };
 
-// Runs `f(handler)` now (it queues kernels, it does not wait for them) and returns a future
-// that completes when everything it queued has finished.  Exceptions thrown by `f` and CUDA
-// errors of the queued work are delivered by future::get(), like the reference's.
+namespace detail {
+
+// how long execute_kernel polls for its kernels before it hands the wait to a thread
+#ifndef SCALIX_B200_FUTURE_POLL_US
+#define SCALIX_B200_FUTURE_POLL_US 25
+#endif
+
+inline std::future<void> ready_future(std::exception_ptr error = nullptr) {
+    std::promise<void> done;
+    if (error) done.set_exception(error);
+    else done.set_value();
+    return done.get_future();
+}
+
+}  // namespace detail
+
+// Runs `f(handler)` on the calling thread — it queues kernels on the persistent per-device
+// streams — and returns the future of /root/reference scalix/execute_kernel.cuh:506-513 with
+// the same observable behaviour: wait_for() reports ready/timeout (never deferred), get()
+// delivers exceptions thrown by `f` and CUDA errors of the queued work, and a future that is
+// DROPPED leaves nothing running (the reference's std::async future blocks in its destructor,
+// relied on at examples/index_generator.cu:78-86).
+//   * Short work (done within SCALIX_B200_FUTURE_POLL_US of polling, i.e. less than a thread
+//     spawn costs): the future is returned already completed.
+//   * Longer work: std::async(std::launch::async) waits for the streams, exactly the
+//     reference's future type — the caller overlaps host work with the kernels, and dropping
+//     the future blocks until they have finished.  The spawn overlaps the kernels themselves.
 template<class F>
 __host__ std::future<void> execute_kernel(F&& f) {
     cuda::detail::ensure_runtime();
@@ -418,11 +442,31 @@ __host__ std::future<void> execute_kernel(F&& f) {
     std::vector<int> devices = used;
     used                     = outer;
     for (int d : devices) detail::launch_record::note(d);
-    return std::async(std::launch::deferred, [devices = std::move(devices), error]() {
-        if (error) std::rethrow_exception(error);
-        if (!devices.empty())
-            cuda::detail::check_rt(sclx_b200_rt_sync_devices(int(devices.size()), devices.data()));
-    });
+    if (devices.empty()) return detail::ready_future(error);
+    auto wait_for_devices = [devices]() {
+        cuda::detail::check_rt(sclx_b200_rt_sync_devices(int(devices.size()), devices.data()));
+    };
+    if (error) {
+        // kernels queued before `f` threw still finish before the future completes
+        try {
+            wait_for_devices();
+        } catch (...) {
+        }
+        return detail::ready_future(error);
+    }
+    const auto t0 = std::chrono::steady_clock::now();
+    do {
+        if (sclx_b200_rt_devices_idle(int(devices.size()), devices.data())) {
+            try {
+                wait_for_devices();  // nothing left to wait for: collects errors, notes the sync
+            } catch (...) {
+                return detail::ready_future(std::current_exception());
+            }
+            return detail::ready_future();
+        }
+    } while (std::chrono::steady_clock::now() - t0
+             < std::chrono::microseconds(SCALIX_B200_FUTURE_POLL_US));
+    return std::async(std::launch::async, wait_for_devices);
 }
 
 }  // namespace sclx

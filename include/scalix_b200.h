@@ -194,6 +194,9 @@ int sclx_b200_array_owner(const void* ptr);       /* logical device holding the 
 
 /* host/device coherence of the mirror */
 int sclx_b200_rt_before_device_access(void);      /* write back host stores, drop host copies */
+/* the range becomes host-resident: readable and writable without faults (syscalls into it
+ * work), pinned for PCIe-rate copies when it covers >= 1/4 of the array, written back as a
+ * whole before the next device access */
 int sclx_b200_rt_prefetch_to_host(const void* ptr, size_t bytes);
 int sclx_b200_rt_quiesce(void);                   /* wait for all device work */
 unsigned long long sclx_b200_rt_host_faults(void);
@@ -204,18 +207,32 @@ int sclx_b200_rt_begin_launch(int ndev, const int* devices);
 int sclx_b200_rt_end_launch(int ndev, const int* devices);
 int sclx_b200_rt_stream_wait(int waiter, int signaller);
 int sclx_b200_rt_sync_devices(int ndev, const int* devices);
+int sclx_b200_rt_devices_idle(int ndev, const int* devices); /* 1 = nothing running (never blocks) */
 
-/* per-device workspaces of the scan / reduce kernels (valid in stream order on that device) */
-int sclx_b200_rt_scan_workspace(int logical, size_t tiles, void** desc, unsigned* epoch);
-int sclx_b200_rt_scan_counters(int logical, void** counters);
-int sclx_b200_rt_reduce_workspace(int logical, size_t bytes, void** partials, void** ticket);
-int sclx_b200_rt_scratch(size_t bytes, void** ptr); /* small peer-visible scratch */
-/* Freed arrays stay mapped in a bounded pool (default 32 GiB, SCLX_B200_POOL_BYTES; 0 = off) and
+/* Workspaces of the scan / reduce kernels, LEASED PER CALL: one lease per (algorithm call,
+ * logical device), used in stream order on that device's stream and returned when the call has
+ * synchronised.  Two calls in flight on different host threads never share partials, tickets
+ * or look-back descriptors (the reference keeps these function-local,
+ * /root/reference scalix/algorithm/reduce_last_dim.cuh:180-211, inclusive_scan.cuh:75-123). */
+int sclx_b200_rt_workspace_acquire(int logical, void** lease);
+int sclx_b200_rt_workspace_release(void* lease, int poisoned); /* poisoned: re-zero tickets first */
+int sclx_b200_rt_workspace_reduce(void* lease, size_t bytes, void** partials, void** ticket);
+/* look-back descriptors: word_bytes 8 (elements <= 4 bytes) or 16 (8-byte elements); each
+ * word size has its own buffer and epoch */
+int sclx_b200_rt_workspace_scan(void* lease, size_t tiles, int word_bytes, void** desc,
+                                unsigned* epoch, void** counters);
+/* small peer-visible scratch (per-partition totals, partial rows), leased per call */
+int sclx_b200_rt_scratch_acquire(size_t bytes, void** ptr);
+int sclx_b200_rt_scratch_release(void* ptr, int poisoned);
+/* Freed arrays stay mapped in a bounded pool (default min(32 GiB, device memory / 8);
+ * SCLX_B200_POOL_BYTES overrides, 0 = off; sclx_b200_rt_pool_release() empties it, e.g. before a
+ * large cudaMalloc of another library; sclx::cuda::query_memory_status counts it as free) and
  * are reused by the next array_create with the same size and placement: building a multi-GiB
  * peer-mapped range costs tens of milliseconds on a multi-GPU node, reusing one costs its
  * zero-fill.  (The reference pays cudaMallocManaged + 4*ndev+2 cudaMemAdvise + ndev prefetches
  * per array, scalix/array.cuh:345,522-612.) */
 size_t sclx_b200_rt_pool_bytes(void);
+size_t sclx_b200_rt_pool_bytes_on(int logical);  /* parked bytes on that device's GPU */
 unsigned long long sclx_b200_rt_pool_hits(void);
 int sclx_b200_rt_pool_release(void);
 /* per-device peer-visible grow-only workspace of sclx::algorithm::gather (exchange form) */

@@ -81,12 +81,16 @@ ABI = {
     "sclx_b200_rt_end_launch": (_i, [_i, _vp]),
     "sclx_b200_rt_stream_wait": (_i, [_i, _i]),
     "sclx_b200_rt_sync_devices": (_i, [_i, _vp]),
-    "sclx_b200_rt_scan_workspace": (_i, [_i, _sz, _pp, _vp]),
-    "sclx_b200_rt_scan_counters": (_i, [_i, _pp]),
-    "sclx_b200_rt_reduce_workspace": (_i, [_i, _sz, _pp, _pp]),
-    "sclx_b200_rt_scratch": (_i, [_sz, _pp]),
+    "sclx_b200_rt_devices_idle": (_i, [_i, _vp]),
+    "sclx_b200_rt_workspace_acquire": (_i, [_i, _pp]),
+    "sclx_b200_rt_workspace_release": (_i, [_vp, _i]),
+    "sclx_b200_rt_workspace_reduce": (_i, [_vp, _sz, _pp, _pp]),
+    "sclx_b200_rt_workspace_scan": (_i, [_vp, _sz, _i, _pp, _vp, _pp]),
+    "sclx_b200_rt_scratch_acquire": (_i, [_sz, _pp]),
+    "sclx_b200_rt_scratch_release": (_i, [_vp, _i]),
     "sclx_b200_rt_exchange_workspace": (_i, [_i, _sz, _pp]),
     "sclx_b200_rt_pool_bytes": (_sz, []),
+    "sclx_b200_rt_pool_bytes_on": (_sz, [_i]),
     "sclx_b200_rt_pool_hits": (C.c_ulonglong, []),
     "sclx_b200_rt_pool_release": (_i, []),
 }

@@ -82,6 +82,7 @@ int rt_fail(cudaError_t e, const char* what) {
 
 // ---- global state --------------------------------------------------------------------------
 constexpr size_t kMirrorChunk = size_t(64) << 10;  // host-mirror coherence granule
+constexpr size_t kPinThreshold = size_t(64) << 20;  // bulk CPU prefetches from this size on pin the mirror
 
 enum chunk_state : unsigned char { kInvalid = 0, kClean = 1, kDirty = 2 };
 
@@ -101,17 +102,40 @@ struct allocation {
     bool overlay_ok = false;
     std::vector<unsigned char> state;  // per mirror chunk
     size_t n_valid = 0;
+    // a bulk prefetch to the CPU pins the mirror pages (cudaHostRegister) so the copies in both
+    // directions run at the PCIe rate; pinned pages are kept until the array is freed
+    bool pinned = false;
+    // sequential host access grows the span a fault brings in: 64 KiB, 128 KiB, ... 16 MiB
+    size_t fault_next = ~size_t(0), fault_span = 1;
+};
+
+// workspaces of the framework-owned kernels, leased per call (never shared by two calls in
+// flight): the reference keeps its partials and mutexes function-local
+// (/root/reference scalix/algorithm/reduce_last_dim.cuh:180-211, inclusive_scan.cuh:75-123)
+struct kernel_workspace {
+    int logical        = 0;
+    void* partials     = nullptr; size_t partial_bytes = 0;
+    unsigned* ticket   = nullptr;  // 256 zeroed bytes: [0] reduce ticket, [32..] scan tile tickets
+    // look-back descriptors, one buffer and one epoch PER WORD SIZE (8-byte words for elements
+    // of <= 4 bytes, 16-byte words for 8-byte elements): a stale word of the other layout must
+    // never be read as a valid {epoch|state, value} pair
+    void* desc[2]      = {nullptr, nullptr};
+    size_t desc_bytes[2] = {0, 0};
+    unsigned epoch[2]  = {0, 0};
 };
 
 struct logical_device {
     int physical        = 0;
     cudaStream_t stream = nullptr;
-    cudaEvent_t done    = nullptr;  // recorded after the latest launch group
+    cudaEvent_t done    = nullptr;  // recorded (lazily) after the latest launch group
+    // launch-group sequence numbers (guarded by g_rt.mu): the latest group that queued work on
+    // this device, and the latest one `done` covers.  `done` is only recorded when a later
+    // group has to wait for it, never in the blocking-call pattern where the host syncs first.
+    unsigned long long last_launch_seq = 0, recorded_seq = 0;
+    unsigned long long host_synced_seq = 0;  // groups <= this were waited for by a host sync of this device
     cudaEvent_t gate    = nullptr;  // recorded by the hub of a launch group once every device's `done` has fired
     int sm_count        = 0;
-    // algorithm workspaces
-    void* scan_desc = nullptr; size_t scan_bytes = 0; unsigned scan_epoch = 0;
-    void* partials = nullptr; size_t partial_bytes = 0; unsigned* ticket = nullptr;
+    std::vector<kernel_workspace*> free_ws;  // leases not in use (guarded by g_rt.mu)
     void* exchange = nullptr; size_t exchange_bytes = 0;  // peer-visible gather-exchange buffers
 };
 
@@ -124,10 +148,14 @@ struct runtime {
     std::map<char*, allocation*> allocs;  // keyed by base
     size_t granularity = size_t(2) << 20;
     std::atomic<size_t> host_valid_chunks{0};
-    std::atomic<bool> unsynced{false};  // launches issued since the last full sync
+    // launch groups issued / covered by a full host synchronisation (monotonic): work is
+    // outstanding while launch_seq != synced_seq.  Two counters instead of a flag so that a
+    // sync on one host thread cannot hide a launch another thread issued meanwhile.
+    std::atomic<unsigned long long> launch_seq{0}, synced_seq{0};
     bool handler_installed = false;
     struct sigaction old_action {};
-    void* scratch = nullptr; size_t scratch_bytes = 0;
+    struct scratch_block { void* ptr; size_t bytes; bool busy; };
+    std::vector<scratch_block> scratch;  // small peer-visible blocks, leased per call
     unsigned long long faults = 0, flushed_chunks = 0;
     // freed arrays kept mapped for reuse (VA + physical pages + peer access + mirror intact):
     // creating a multi-GiB peer-mapped range costs tens of ms on a multi-GPU node, reusing one
@@ -175,8 +203,14 @@ int ensure_init() {
         RT(cudaEventCreateWithFlags(&ld.done, cudaEventDisableTiming));
         RT(cudaEventCreateWithFlags(&ld.gate, cudaEventDisableTiming));
         RT(cudaDeviceGetAttribute(&ld.sm_count, cudaDevAttrMultiProcessorCount, ld.physical));
-        RT(cudaMalloc(&ld.ticket, 256));
-        RT(cudaMemset(ld.ticket, 0, 256));
+    }
+    if (!getenv("SCLX_B200_POOL_BYTES")) {
+        // parked arrays hold device memory other allocators in the process cannot see: keep the
+        // default cap to an eighth of the device
+        size_t free_b = 0, total_b = 0;
+        RT(cudaSetDevice(g_rt.dev[0].physical));
+        if (cudaMemGetInfo(&free_b, &total_b) == cudaSuccess && total_b / 8 < g_rt.pool_cap)
+            g_rt.pool_cap = total_b / 8;
     }
     if (g_rt.emulated == 0) {
         // NVLink/NVSwitch peer access for cudaMalloc'd workspaces (VMM ranges carry their own ACLs)
@@ -218,9 +252,18 @@ allocation* find_alloc(const void* p) {
 int physical_of(int logical) { return g_rt.dev[logical].physical; }
 
 // ---- host mirror ---------------------------------------------------------------------------
+bool work_outstanding() { return g_rt.launch_seq.load() != g_rt.synced_seq.load(); }
+
+// every launch group numbered <= seq has been waited for by the host
+void note_synced(unsigned long long seq) {
+    unsigned long long cur = g_rt.synced_seq.load();
+    while (cur < seq && !g_rt.synced_seq.compare_exchange_weak(cur, seq)) {}
+}
+
 int sync_all_streams() {
     int cur = 0;
     cudaGetDevice(&cur);
+    const unsigned long long seq = g_rt.launch_seq.load();
     for (auto& ld : g_rt.dev) {
         RT(cudaSetDevice(ld.physical));
         RT(cudaStreamSynchronize(ld.stream));
@@ -231,7 +274,7 @@ int sync_all_streams() {
         RT(cudaDeviceSynchronize());
     }
     RT(cudaSetDevice(cur));
-    g_rt.unsynced.store(false);
+    note_synced(seq);
     return 0;
 }
 
@@ -259,18 +302,56 @@ int for_each_piece(const allocation& al, size_t off, size_t len, F&& f) {
     return 0;
 }
 
-// bring chunks [c0, c1) of the host mirror up to date (device -> host)
+// One transfer between the mirror and device memory, [off, off+len) of `al`, split at
+// physical-run boundaries.  A pinned mirror moves each piece asynchronously on its owner's
+// stream (several GPUs = several PCIe links at once) and waits for all of them at the end; a
+// pageable one uses blocking copies.
+int copy_pieces(allocation& al, size_t off, size_t len, bool to_host) {
+    if (len == 0) return 0;
+    if (!al.pinned)
+        return for_each_piece(al, off, len, [&](size_t o, size_t piece) -> int {
+            if (to_host) RT(cudaMemcpy(al.alias + o, al.base + o, piece, cudaMemcpyDeviceToHost));
+            else RT(cudaMemcpy(al.base + o, al.alias + o, piece, cudaMemcpyHostToDevice));
+            return 0;
+        });
+    int cur = 0;
+    cudaGetDevice(&cur);
+    std::vector<int> used;
+    int rc = for_each_piece(al, off, len, [&](size_t o, size_t piece) -> int {
+        const int owner    = owner_of(al, o);
+        logical_device& ld = g_rt.dev[owner];
+        RT(cudaSetDevice(ld.physical));
+        if (to_host) RT(cudaMemcpyAsync(al.alias + o, al.base + o, piece, cudaMemcpyDeviceToHost, ld.stream));
+        else RT(cudaMemcpyAsync(al.base + o, al.alias + o, piece, cudaMemcpyHostToDevice, ld.stream));
+        if (std::find(used.begin(), used.end(), owner) == used.end()) used.push_back(owner);
+        return 0;
+    });
+    for (int d : used) {
+        cudaSetDevice(g_rt.dev[d].physical);
+        cudaError_t e = cudaStreamSynchronize(g_rt.dev[d].stream);
+        if (e != cudaSuccess && rc == 0) rc = rt_fail(e, "cudaStreamSynchronize");
+    }
+    cudaSetDevice(cur);
+    return rc;
+}
+
+// bring chunks [c0, c1) of the host mirror up to date (device -> host); `for_write` leaves them
+// writable and marked dirty (they go back to the device before its next access)
 int fetch_chunks(allocation& al, size_t c0, size_t c1, bool for_write) {
     // coalesce invalid chunks into runs so a bulk prefetch is one copy per physical run
     size_t c = c0;
     bool synced = false;
     while (c < c1) {
         if (al.state[c] != kInvalid) {
-            if (for_write && al.state[c] == kClean) {
-                al.state[c] = kDirty;
-                mprotect(al.base + c * kMirrorChunk, kMirrorChunk, PROT_READ | PROT_WRITE);
+            size_t e = c;
+            while (e < c1 && al.state[e] != kInvalid) ++e;
+            if (for_write) {
+                bool any_clean = false;
+                for (size_t k = c; k < e; ++k)
+                    if (al.state[k] == kClean) { al.state[k] = kDirty; any_clean = true; }
+                if (any_clean) mprotect(al.base + c * kMirrorChunk, (e - c) * kMirrorChunk, PROT_READ | PROT_WRITE);
             }
-            ++c;
+            c = e;
             continue;
         }
         size_t e = c;
@@ -281,11 +362,7 @@ int fetch_chunks(allocation& al, size_t c0, size_t c1, bool for_write) {
         }
         size_t off = c * kMirrorChunk, len = (e - c) * kMirrorChunk;
         if (off + len > al.va_bytes) len = al.va_bytes - off;
-        if (int rc = for_each_piece(al, off, len, [&](size_t o, size_t piece) -> int {
-                RT(cudaMemcpy(al.alias + o, al.base + o, piece, cudaMemcpyDeviceToHost));
-                return 0;
-            }))
-            return rc;
+        if (int rc = copy_pieces(al, off, len, /*to_host=*/true)) return rc;
         for (size_t k = c; k < e; ++k) al.state[k] = for_write ? kDirty : kClean;
         mprotect(al.base + off, (e - c) * kMirrorChunk, for_write ? (PROT_READ | PROT_WRITE) : PROT_READ);
         al.n_valid += e - c;
@@ -312,24 +389,25 @@ int flush_and_invalidate(allocation& al) {
             while (f < e && al.state[f] == kDirty) ++f;
             size_t off = d * kMirrorChunk, len = (f - d) * kMirrorChunk;
             if (off + len > al.va_bytes) len = al.va_bytes - off;
-            if (int rc = for_each_piece(al, off, len, [&](size_t o, size_t piece) -> int {
-                    RT(cudaMemcpy(al.base + o, al.alias + o, piece, cudaMemcpyHostToDevice));
-                    return 0;
-                }))
-                return rc;
+            if (int rc = copy_pieces(al, off, len, /*to_host=*/false)) return rc;
             g_rt.flushed_chunks += f - d;
             d = f;
         }
         size_t off = c * kMirrorChunk, len = (e - c) * kMirrorChunk;
         mprotect(al.base + off, len, PROT_NONE);
-        if (al.memfd >= 0) fallocate(al.memfd, FALLOC_FL_PUNCH_HOLE | FALLOC_FL_KEEP_SIZE, off, len);
+        // pinned pages stay (the registration holds them); pageable ones go back to the kernel
+        if (al.memfd >= 0 && !al.pinned) fallocate(al.memfd, FALLOC_FL_PUNCH_HOLE | FALLOC_FL_KEEP_SIZE, off, len);
         for (size_t k = c; k < e; ++k) al.state[k] = kInvalid;
         g_rt.host_valid_chunks.fetch_sub(e - c);
         c = e;
     }
-    al.n_valid = 0;
+    al.n_valid    = 0;
+    al.fault_next = ~size_t(0);
+    al.fault_span = 1;
     return 0;
 }
+
+constexpr size_t kMaxFaultSpan = 256;  // chunks: 16 MiB
 
 void on_segv(int sig, siginfo_t* si, void* uctx) {
     char* addr = (char*)si->si_addr;
@@ -342,9 +420,18 @@ void on_segv(int sig, siginfo_t* si, void* uctx) {
 #if defined(__x86_64__)
             write = (((ucontext_t*)uctx)->uc_mcontext.gregs[REG_ERR] & 2) != 0;
 #endif
+            const size_t nchunks = al->state.size();
             size_t c = size_t(addr - al->base) / kMirrorChunk;
+            // a fault right behind the previous one is a sequential sweep: double the span
+            size_t span = 1;
+            if (c == al->fault_next) span = std::min(al->fault_span * 2, kMaxFaultSpan);
+            const size_t c1 = std::min(c + span, nchunks);
             ++g_rt.faults;
-            if (fetch_chunks(*al, c, c + 1, write) == 0) handled = true;
+            if (fetch_chunks(*al, c, c1, write) == 0) {
+                handled        = true;
+                al->fault_next = c1;
+                al->fault_span = span;
+            }
         }
     }
     if (handled) return;
@@ -466,7 +553,14 @@ int unmap_runs(allocation& al) {
 }
 
 // tear an allocation down completely (mappings, physical pages, mirror, reservation)
+void unpin_mirror(allocation& al) {
+    if (!al.pinned) return;
+    if (cudaHostUnregister(al.alias) != cudaSuccess) cudaGetLastError();
+    al.pinned = false;
+}
+
 int destroy_allocation(allocation* al) {
+    unpin_mirror(*al);
     if (al->overlay_ok) {
         // give the range back to a plain reservation before the driver unmaps it
         mmap(al->base, al->va_bytes, PROT_NONE, MAP_PRIVATE | MAP_ANONYMOUS | MAP_FIXED | MAP_NORESERVE, -1, 0);
@@ -485,6 +579,11 @@ int destroy_allocation(allocation* al) {
 // forget every host-valid chunk WITHOUT writing anything back (the array is dead)
 void drop_mirror(allocation& al) {
     if (!al.overlay_ok) return;
+    const bool was_pinned = al.pinned;
+    unpin_mirror(al);
+    if (was_pinned && al.memfd >= 0) fallocate(al.memfd, FALLOC_FL_PUNCH_HOLE | FALLOC_FL_KEEP_SIZE, 0, (off_t)al.va_bytes);
+    al.fault_next = ~size_t(0);
+    al.fault_span = 1;
     const size_t nchunks = al.state.size();
     size_t c = 0;
     while (c < nchunks) {
@@ -647,7 +746,12 @@ int sclx_b200_array_free(void* base) {
     auto it = g_rt.allocs.find((char*)base);
     if (it == g_rt.allocs.end()) return fail(SCLX_E_INVALID_ARGUMENT, "array_free: unknown pointer");
     allocation* al = it->second;
-    if (g_rt.unsynced.load()) sync_all_streams();  // kernels in flight may still use it
+    if (work_outstanding()) {  // kernels in flight may still use it
+        const unsigned long long synced = g_rt.synced_seq.load();
+        bool busy = false;
+        for (auto& ld : g_rt.dev) busy |= ld.last_launch_seq > synced && ld.last_launch_seq > ld.host_synced_seq;
+        if (busy) sync_all_streams();
+    }
     if (al->n_valid) {
         g_rt.host_valid_chunks.fetch_sub(al->n_valid);
         al->n_valid = 0;
@@ -739,7 +843,12 @@ int sclx_b200_rt_before_device_access(void) {
     return 0;
 }
 
-// bulk "prefetch to the CPU" (array::prefetch_async({cpu_device_id})): one large copy
+// bulk "prefetch to the CPU" (array::prefetch_async({cpu_device_id})): the range becomes
+// HOST-RESIDENT — fetched in large copies, readable AND writable without further faults
+// (so read(2)/fread/recv into it work, as they do on the reference's managed memory,
+// /root/reference scalix/array.cuh:241-248,647-711), and written back as a whole before the
+// next device access, like migrated pages.  A prefetch of 64 MiB or more that covers at least a
+// quarter of the array pins the mirror so both directions run at the PCIe rate.
 int sclx_b200_rt_prefetch_to_host(const void* ptr, size_t bytes) {
     if (int rc = ensure_init()) return rc;
     std::lock_guard<std::recursive_mutex> lock(g_rt.mu);
@@ -747,7 +856,11 @@ int sclx_b200_rt_prefetch_to_host(const void* ptr, size_t bytes) {
     if (!al || !al->overlay_ok || bytes == 0) return 0;
     size_t off = size_t((char*)ptr - al->base);
     size_t c0 = off / kMirrorChunk, c1 = (std::min(off + bytes, al->va_bytes) + kMirrorChunk - 1) / kMirrorChunk;
-    return fetch_chunks(*al, c0, c1, false);
+    if (!al->pinned && bytes >= kPinThreshold && bytes >= al->bytes / 4 && !getenv("SCLX_B200_NO_PIN")) {
+        if (cudaHostRegister(al->alias, al->va_bytes, cudaHostRegisterPortable) == cudaSuccess) al->pinned = true;
+        else cudaGetLastError();
+    }
+    return fetch_chunks(*al, c0, c1, /*for_write=*/true);
 }
 
 int sclx_b200_rt_quiesce(void) {
@@ -764,48 +877,45 @@ int sclx_b200_rt_quiesce(void) {
 int sclx_b200_rt_begin_launch(int ndev, const int* devices) {
     if (int rc = ensure_init()) return rc;
     if (int rc = sclx_b200_rt_before_device_access()) return rc;
-    if (!g_rt.unsynced.load() || g_rt.dev.size() == 1) return 0;
+    if (!work_outstanding() || g_rt.dev.size() == 1) return 0;
     std::lock_guard<std::recursive_mutex> lock(g_rt.mu);
-    int cur = 0;
-    cudaGetDevice(&cur);
-    if (ndev <= 2) {
-        for (int i = 0; i < ndev; ++i) {
-            logical_device& me = g_rt.dev[devices[i]];
-            RT(cudaSetDevice(me.physical));
-            for (size_t o = 0; o < g_rt.dev.size(); ++o)
-                if ((int)o != devices[i]) RT(cudaStreamWaitEvent(me.stream, g_rt.dev[o].done, 0));
+    // events and stream waits do not need the stream's device to be current
+    const unsigned long long synced = g_rt.synced_seq.load();
+    std::vector<int> busy;  // devices with work the host has not waited for
+    for (size_t o = 0; o < g_rt.dev.size(); ++o) {
+        logical_device& ld = g_rt.dev[o];
+        if (ld.last_launch_seq <= synced || ld.last_launch_seq <= ld.host_synced_seq) continue;
+        if (ld.recorded_seq < ld.last_launch_seq) {
+            RT(cudaEventRecord(ld.done, ld.stream));
+            ld.recorded_seq = ld.last_launch_seq;
         }
+        busy.push_back((int)o);
+    }
+    if (busy.empty()) return 0;
+    auto waits_for_busy = [&](logical_device& me, int self) -> int {
+        for (int o : busy)
+            if (o != self) RT(cudaStreamWaitEvent(me.stream, g_rt.dev[o].done, 0));
+        return 0;
+    };
+    if (ndev <= 2 || busy.size() <= 1) {
+        for (int i = 0; i < ndev; ++i)
+            if (int rc = waits_for_busy(g_rt.dev[devices[i]], devices[i])) return rc;
     } else {
         // O(N) instead of O(N^2) driver calls: the first participant (hub) waits for every
-        // other device, records its gate, the other participants wait for the gate
+        // busy device, records its gate, the other participants wait for the gate
         logical_device& hub = g_rt.dev[devices[0]];
-        RT(cudaSetDevice(hub.physical));
-        for (size_t o = 0; o < g_rt.dev.size(); ++o)
-            if ((int)o != devices[0]) RT(cudaStreamWaitEvent(hub.stream, g_rt.dev[o].done, 0));
+        if (int rc = waits_for_busy(hub, devices[0])) return rc;
         RT(cudaEventRecord(hub.gate, hub.stream));
-        for (int i = 1; i < ndev; ++i) {
-            logical_device& me = g_rt.dev[devices[i]];
-            RT(cudaSetDevice(me.physical));
-            RT(cudaStreamWaitEvent(me.stream, hub.gate, 0));
-        }
+        for (int i = 1; i < ndev; ++i) RT(cudaStreamWaitEvent(g_rt.dev[devices[i]].stream, hub.gate, 0));
     }
-    RT(cudaSetDevice(cur));
     return 0;
 }
 
 int sclx_b200_rt_end_launch(int ndev, const int* devices) {
     std::lock_guard<std::recursive_mutex> lock(g_rt.mu);
-    if (g_rt.dev.size() > 1) {
-        int cur = 0;
-        cudaGetDevice(&cur);
-        for (int i = 0; i < ndev; ++i) {
-            logical_device& me = g_rt.dev[devices[i]];
-            RT(cudaSetDevice(me.physical));
-            RT(cudaEventRecord(me.done, me.stream));
-        }
-        RT(cudaSetDevice(cur));
-    }
-    g_rt.unsynced.store(true);
+    const unsigned long long seq = g_rt.launch_seq.fetch_add(1) + 1;
+    for (int i = 0; i < ndev; ++i)
+        if (devices[i] >= 0 && devices[i] < (int)g_rt.dev.size()) g_rt.dev[devices[i]].last_launch_seq = seq;
     return 0;
 }
 
@@ -813,109 +923,190 @@ int sclx_b200_rt_end_launch(int ndev, const int* devices) {
 int sclx_b200_rt_stream_wait(int waiter, int signaller) {
     if (int rc = ensure_init()) return rc;
     if (waiter == signaller) return 0;
+    if (waiter < 0 || signaller < 0 || waiter >= (int)g_rt.dev.size() || signaller >= (int)g_rt.dev.size())
+        return fail(SCLX_E_INVALID_ARGUMENT, "stream_wait: device id out of range");
     std::lock_guard<std::recursive_mutex> lock(g_rt.mu);
-    int cur = 0;
-    cudaGetDevice(&cur);
     logical_device& s = g_rt.dev[signaller];
     logical_device& w = g_rt.dev[waiter];
-    RT(cudaSetDevice(s.physical));
     RT(cudaEventRecord(s.done, s.stream));
-    RT(cudaSetDevice(w.physical));
+    s.recorded_seq = s.last_launch_seq;
     RT(cudaStreamWaitEvent(w.stream, s.done, 0));
-    RT(cudaSetDevice(cur));
     return 0;
 }
 
 int sclx_b200_rt_sync_devices(int ndev, const int* devices) {
     if (int rc = ensure_init()) return rc;
-    int cur = 0;
-    cudaGetDevice(&cur);
-    cudaError_t first = cudaSuccess;
+    const int total = (int)g_rt.dev.size();
+    if (ndev < 0 || (ndev > 0 && !devices)) return fail(SCLX_E_INVALID_ARGUMENT, "sync_devices: bad device list");
+    unsigned long long seen = 0;  // bitmap of distinct logical devices (lists may repeat ids)
     for (int i = 0; i < ndev; ++i) {
-        logical_device& me = g_rt.dev[devices[i]];
-        cudaSetDevice(me.physical);
-        cudaError_t e = cudaStreamSynchronize(me.stream);
+        if (devices[i] < 0 || devices[i] >= total || devices[i] >= 64)
+            return fail(SCLX_E_INVALID_ARGUMENT, "sync_devices: device id out of range");
+        seen |= 1ull << devices[i];
+    }
+    const unsigned long long seq = g_rt.launch_seq.load();
+    cudaError_t first = cudaSuccess;
+    int distinct = 0;
+    for (int d = 0; d < total && d < 64; ++d) {
+        if (!(seen >> d & 1)) continue;
+        ++distinct;
+        cudaError_t e = cudaStreamSynchronize(g_rt.dev[d].stream);
         if (e != cudaSuccess && first == cudaSuccess) first = e;
     }
-    cudaSetDevice(cur);
     if (first != cudaSuccess) return rt_fail(first, "cudaStreamSynchronize");
-    if (ndev == (int)g_rt.dev.size()) g_rt.unsynced.store(false);
+    // only a sync of EVERY logical device covers all the groups issued before it started
+    if (distinct == total) note_synced(seq);
+    else {
+        std::lock_guard<std::recursive_mutex> lock(g_rt.mu);
+        for (int d = 0; d < total && d < 64; ++d)
+            if ((seen >> d & 1) && g_rt.dev[d].host_synced_seq < seq) g_rt.dev[d].host_synced_seq = seq;
+    }
     return 0;
 }
 
-// ---- algorithm workspaces (per logical device; used in stream order on that device's stream) --
-int sclx_b200_rt_scan_workspace(int logical, size_t tiles, void** desc, unsigned* epoch) {
+// 1 when every stream in the list is idle, 0 when work is still running (never blocks)
+int sclx_b200_rt_devices_idle(int ndev, const int* devices) {
+    if (ensure_init()) return 0;
+    const int total = (int)g_rt.dev.size();
+    for (int i = 0; i < ndev; ++i) {
+        if (devices[i] < 0 || devices[i] >= total) continue;
+        // running, or failed: the blocking sync reports the error
+        if (cudaStreamQuery(g_rt.dev[devices[i]].stream) != cudaSuccess) return 0;
+    }
+    return 1;
+}
+
+// ---- algorithm workspaces: leased per call ---------------------------------------------------
+// A lease belongs to ONE algorithm call on ONE logical device; its kernels use it in stream
+// order on that device's stream.  Two calls in flight (two host threads) never share partial
+// buffers, tickets or look-back descriptors.
+int sclx_b200_rt_workspace_acquire(int logical, void** lease) {
     if (int rc = ensure_init()) return rc;
-    if (logical < 0 || logical >= (int)g_rt.dev.size()) return fail(SCLX_E_INVALID_ARGUMENT, "bad device");
+    if (logical < 0 || logical >= (int)g_rt.dev.size() || !lease) return fail(SCLX_E_INVALID_ARGUMENT, "bad device");
     std::lock_guard<std::recursive_mutex> lock(g_rt.mu);
     logical_device& ld = g_rt.dev[logical];
+    if (!ld.free_ws.empty()) {
+        *lease = ld.free_ws.back();
+        ld.free_ws.pop_back();
+        return 0;
+    }
     int cur = 0;
     cudaGetDevice(&cur);
     RT(cudaSetDevice(ld.physical));
-    const size_t want = tiles * 16 + 4096;
-    if (ld.scan_bytes < want) {
-        if (ld.scan_desc) { RT(cudaStreamSynchronize(ld.stream)); RT(cudaFree(ld.scan_desc)); }
-        ld.scan_bytes = want + want / 2;
-        RT(cudaMalloc(&ld.scan_desc, ld.scan_bytes));
-        RT(cudaMemsetAsync(ld.scan_desc, 0, ld.scan_bytes, ld.stream));
-        ld.scan_epoch = 0;
-    }
-    if (++ld.scan_epoch >= (1u << 30)) {
-        RT(cudaMemsetAsync(ld.scan_desc, 0, ld.scan_bytes, ld.stream));
-        ld.scan_epoch = 1;
-    }
-    RT(cudaSetDevice(cur));
-    *desc  = ld.scan_desc;
-    *epoch = ld.scan_epoch;
+    auto* ws    = new kernel_workspace;
+    ws->logical = logical;
+    cudaError_t e = cudaMalloc(&ws->ticket, 256);
+    if (e == cudaSuccess) e = cudaMemset(ws->ticket, 0, 256);
+    cudaSetDevice(cur);
+    if (e != cudaSuccess) { delete ws; return rt_fail(e, "workspace allocation"); }
+    *lease = ws;
     return 0;
 }
 
-// tile-ticket counters of the streaming scan (zero-initialised, self-resetting)
-int sclx_b200_rt_scan_counters(int logical, void** counters) {
-    if (int rc = ensure_init()) return rc;
-    if (logical < 0 || logical >= (int)g_rt.dev.size() || !counters)
-        return fail(SCLX_E_INVALID_ARGUMENT, "bad device");
-    *counters = g_rt.dev[logical].ticket + 32;
-    return 0;
-}
-
-int sclx_b200_rt_reduce_workspace(int logical, size_t bytes, void** partials, void** ticket) {
-    if (int rc = ensure_init()) return rc;
-    if (logical < 0 || logical >= (int)g_rt.dev.size()) return fail(SCLX_E_INVALID_ARGUMENT, "bad device");
+// `poisoned`: the call ended in an exception and may have left tickets half-way: wait for the
+// device and zero them again before the lease is reused
+int sclx_b200_rt_workspace_release(void* lease, int poisoned) {
+    if (!lease) return 0;
     std::lock_guard<std::recursive_mutex> lock(g_rt.mu);
-    logical_device& ld = g_rt.dev[logical];
+    auto* ws = static_cast<kernel_workspace*>(lease);
+    if (poisoned && ws->ticket) {
+        logical_device& ld = g_rt.dev[ws->logical];
+        cudaStreamSynchronize(ld.stream);
+        cudaMemcpy(ws->ticket, std::vector<unsigned char>(256, 0).data(), 256, cudaMemcpyHostToDevice);
+        cudaGetLastError();
+    }
+    g_rt.dev[ws->logical].free_ws.push_back(ws);
+    return 0;
+}
+
+// partials + ticket of reduce / reduce_last_dim / map_reduce
+int sclx_b200_rt_workspace_reduce(void* lease, size_t bytes, void** partials, void** ticket) {
+    if (!lease) return fail(SCLX_E_INVALID_ARGUMENT, "null workspace lease");
+    auto* ws           = static_cast<kernel_workspace*>(lease);
+    logical_device& ld = g_rt.dev[ws->logical];
+    if (ws->partial_bytes < bytes) {
+        int cur = 0;
+        cudaGetDevice(&cur);
+        RT(cudaSetDevice(ld.physical));
+        // the holder's own earlier kernels may still read the old buffer
+        if (ws->partials) { RT(cudaStreamSynchronize(ld.stream)); RT(cudaFree(ws->partials)); ws->partials = nullptr; }
+        ws->partial_bytes = bytes + bytes / 2 + 4096;
+        RT(cudaMalloc(&ws->partials, ws->partial_bytes));
+        RT(cudaSetDevice(cur));
+    }
+    *partials = ws->partials;
+    *ticket   = ws->ticket;
+    return 0;
+}
+
+// look-back descriptors (`word_bytes` = 8 or 16, one buffer and epoch each) + tile-ticket
+// counters of the scan kernels
+int sclx_b200_rt_workspace_scan(void* lease, size_t tiles, int word_bytes, void** desc, unsigned* epoch,
+                                void** counters) {
+    if (!lease) return fail(SCLX_E_INVALID_ARGUMENT, "null workspace lease");
+    if (word_bytes != 8 && word_bytes != 16) return fail(SCLX_E_INVALID_ARGUMENT, "descriptor words are 8 or 16 bytes");
+    auto* ws           = static_cast<kernel_workspace*>(lease);
+    logical_device& ld = g_rt.dev[ws->logical];
+    const int k        = word_bytes == 8 ? 0 : 1;
     int cur = 0;
     cudaGetDevice(&cur);
     RT(cudaSetDevice(ld.physical));
-    if (ld.partial_bytes < bytes) {
-        if (ld.partials) { RT(cudaStreamSynchronize(ld.stream)); RT(cudaFree(ld.partials)); }
-        ld.partial_bytes = bytes + bytes / 2 + 4096;
-        RT(cudaMalloc(&ld.partials, ld.partial_bytes));
+    const size_t want = tiles * size_t(word_bytes) + 4096;
+    if (ws->desc_bytes[k] < want) {
+        if (ws->desc[k]) { RT(cudaStreamSynchronize(ld.stream)); RT(cudaFree(ws->desc[k])); ws->desc[k] = nullptr; }
+        ws->desc_bytes[k] = want + want / 2;
+        RT(cudaMalloc(&ws->desc[k], ws->desc_bytes[k]));
+        RT(cudaMemsetAsync(ws->desc[k], 0, ws->desc_bytes[k], ld.stream));
+        ws->epoch[k] = 0;
+    }
+    if (++ws->epoch[k] >= (1u << 30)) {
+        RT(cudaMemsetAsync(ws->desc[k], 0, ws->desc_bytes[k], ld.stream));
+        ws->epoch[k] = 1;
     }
     RT(cudaSetDevice(cur));
-    *partials = ld.partials;
-    *ticket   = ld.ticket;
+    *desc  = ws->desc[k];
+    *epoch = ws->epoch[k];
+    if (counters) *counters = ws->ticket + 32;
     return 0;
 }
 
-// small peer-visible scratch (per-partition totals, partial rows): a VMM array on device 0
-int sclx_b200_rt_scratch(size_t bytes, void** ptr) {
+// small peer-visible scratch (per-partition totals, partial rows): VMM arrays on device 0,
+// leased per call and returned when the call has synchronised
+int sclx_b200_rt_scratch_acquire(size_t bytes, void** ptr) {
     if (int rc = ensure_init()) return rc;
+    if (!ptr) return fail(SCLX_E_INVALID_ARGUMENT, "scratch: null out pointer");
     std::lock_guard<std::recursive_mutex> lock(g_rt.mu);
-    if (g_rt.scratch_bytes < bytes) {
-        if (g_rt.scratch) {
-            sync_all_streams();
-            sclx_b200_array_free(g_rt.scratch);
-            g_rt.scratch = nullptr;
+    for (auto& blk : g_rt.scratch)
+        if (!blk.busy && blk.bytes >= bytes) {
+            blk.busy = true;
+            *ptr     = blk.ptr;
+            return 0;
         }
-        int dev0 = 0;
-        size_t z = 0;
-        size_t want = std::max<size_t>(bytes, size_t(1) << 20);
-        if (int rc = sclx_b200_array_create(want, 1, &dev0, &z, &g_rt.scratch)) return rc;
-        g_rt.scratch_bytes = want;
-    }
-    *ptr = g_rt.scratch;
+    int dev0 = 0;
+    size_t z = 0;
+    const size_t want = std::max<size_t>(bytes, size_t(1) << 20);
+    void* block = nullptr;
+    if (int rc = sclx_b200_array_create(want, 1, &dev0, &z, &block)) return rc;
+    g_rt.scratch.push_back({block, want, true});
+    *ptr = block;
     return 0;
+}
+
+int sclx_b200_rt_scratch_release(void* ptr, int poisoned) {
+    if (!ptr) return 0;
+    std::lock_guard<std::recursive_mutex> lock(g_rt.mu);
+    for (auto& blk : g_rt.scratch)
+        if (blk.ptr == ptr) {
+            if (poisoned) {  // arrival counters may be half-way: zero the block once it is idle
+                sync_all_streams();
+                cudaMemset(blk.ptr, 0, blk.bytes);
+                cudaDeviceSynchronize();
+                cudaGetLastError();
+            }
+            blk.busy = false;
+            return 0;
+        }
+    return fail(SCLX_E_INVALID_ARGUMENT, "scratch_release: unknown block");
 }
 
 // per-device, peer-visible, grow-only workspace of the exchange gather (request queues,
@@ -945,6 +1136,16 @@ unsigned long long sclx_b200_rt_host_faults(void) { return g_rt.faults; }
 
 // array pool: bytes parked / reuse counters / explicit release (e.g. before a large cudaMalloc)
 size_t sclx_b200_rt_pool_bytes(void) { return g_rt.pool_bytes; }
+// device memory of `logical`'s GPU held by parked arrays (query_memory_status adds it to `free`)
+size_t sclx_b200_rt_pool_bytes_on(int logical) {
+    if (!g_rt.initialised || logical < 0 || logical >= (int)g_rt.dev.size()) return 0;
+    std::lock_guard<std::recursive_mutex> lock(g_rt.mu);
+    size_t sum = 0;
+    for (allocation* al : g_rt.pool)
+        for (auto& r : al->runs)
+            if (physical_of(r.logical_device) == physical_of(logical)) sum += r.bytes;
+    return sum;
+}
 unsigned long long sclx_b200_rt_pool_hits(void) { return g_rt.pool_hits; }
 int sclx_b200_rt_pool_release(void) {
     std::lock_guard<std::recursive_mutex> lock(g_rt.mu);

@@ -11,6 +11,7 @@
 #include <atomic>
 #include <cstdio>
 #include <cstring>
+#include <map>
 #include <mutex>
 #include <string>
 #include <vector>
@@ -74,24 +75,30 @@ struct op_min {
     }
 };
 
-// ---- per-device workspace ---------------------------------------------------------
-struct device_state {
-    std::mutex mu;
-    int sm_count        = 0;
-    void* scan_desc     = nullptr;
-    size_t scan_bytes   = 0;
-    unsigned scan_epoch = 0;
-    void* partials      = nullptr;
-    size_t part_bytes   = 0;
-    unsigned* ticket    = nullptr;
-    scan_stream_counters* scan_counters = nullptr;  // tile tickets of the streaming scan
-    void* ptr_table     = nullptr;  // small device scratch
-    cudaStream_t last_stream = nullptr;
-    bool has_last            = false;
-    cudaEvent_t last_done    = nullptr;
+// ---- workspaces: one per (device, stream) ----------------------------------------------
+// The C ABI accepts arbitrary caller streams.  Kernels on one stream use that stream's
+// workspace in stream order; two streams never share partials, tickets or look-back
+// descriptors, so concurrent calls on different streams neither race nor serialise.
+struct stream_workspace {
+    void* partials     = nullptr;
+    size_t part_bytes  = 0;
+    unsigned* ticket   = nullptr;  // 256 zeroed bytes: [0] reduce ticket, [32..] scan tile tickets
+    // look-back descriptors: one buffer and epoch per word size (8-byte words for elements of
+    // <= 4 bytes, 16-byte words for 8-byte elements) — a stale word of the other layout must
+    // never be decoded as {epoch|state, value}
+    void* desc[2]        = {nullptr, nullptr};
+    size_t desc_bytes[2] = {0, 0};
+    unsigned epoch[2]    = {0, 0};
 };
 
-constexpr int kMaxDevices = 64;
+struct device_state {
+    std::mutex mu;
+    int sm_count = 0;
+    std::map<cudaStream_t, stream_workspace> streams;
+};
+
+constexpr int kMaxDevices        = 64;
+constexpr size_t kMaxStreamSlots = 256;  // workspaces kept per device before a reset
 device_state g_dev[kMaxDevices];
 
 int current_state(device_state** out) {
@@ -103,35 +110,40 @@ int current_state(device_state** out) {
     if (st.sm_count == 0) {
         int sms = 0;
         SCLX_CUDA(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
-        SCLX_CUDA(cudaEventCreateWithFlags(&st.last_done, cudaEventDisableTiming));
-        SCLX_CUDA(cudaMalloc(&st.ticket, 256));
-        SCLX_CUDA(cudaMemset(st.ticket, 0, 256));
-        st.scan_counters = reinterpret_cast<scan_stream_counters*>(st.ticket + 32);
         st.sm_count = sms;
     }
     *out = &st;
     return 0;
 }
 
-// The workspace is shared by all launches on a device.  Launches on one stream are
-// ordered by the stream; a launch on a different stream first waits for the previous
-// user of the workspace.
-int order_after_previous(device_state& st, cudaStream_t stream) {
-    if (st.has_last && st.last_stream != stream)
-        SCLX_CUDA(cudaStreamWaitEvent(stream, st.last_done, 0));
-    return 0;
-}
-int mark_use(device_state& st, cudaStream_t stream) {
-    SCLX_CUDA(cudaEventRecord(st.last_done, stream));
-    st.last_stream = stream;
-    st.has_last    = true;
+// the workspace of `stream` on the current device (call with st.mu held)
+int workspace_for(device_state& st, cudaStream_t stream, stream_workspace** out) {
+    auto it = st.streams.find(stream);
+    if (it == st.streams.end()) {
+        if (st.streams.size() >= kMaxStreamSlots) {
+            // streams come and go: start over once nothing can still be using the old slots
+            SCLX_CUDA(cudaDeviceSynchronize());
+            for (auto& kv : st.streams) {
+                cudaFree(kv.second.partials);
+                cudaFree(kv.second.ticket);
+                cudaFree(kv.second.desc[0]);
+                cudaFree(kv.second.desc[1]);
+            }
+            st.streams.clear();
+        }
+        stream_workspace ws;
+        SCLX_CUDA(cudaMalloc(&ws.ticket, 256));
+        SCLX_CUDA(cudaMemsetAsync(ws.ticket, 0, 256, stream));
+        it = st.streams.emplace(stream, ws).first;
+    }
+    *out = &it->second;
     return 0;
 }
 
 int ensure_bytes(void** p, size_t* have, size_t want, bool zero, cudaStream_t stream) {
     if (*have >= want) return 0;
     if (*p) {
-        SCLX_CUDA(cudaDeviceSynchronize());
+        SCLX_CUDA(cudaStreamSynchronize(stream));  // only this stream's kernels use the buffer
         SCLX_CUDA(cudaFree(*p));
         *p    = nullptr;
         *have = 0;
@@ -224,17 +236,19 @@ int launch_scan(const T* in, T* out, size_t n, const T* lower, int n_lower, T* t
     const size_t tile_items = aligned ? scfg::tile_items : rcfg::tile_items;
     const size_t tiles      = (n + tile_items - 1) / tile_items;
     if (tiles > 0x7fffffffull) return fail(SCLX_E_INVALID_ARGUMENT, "scan: partition too large");
-    if (int rc = order_after_previous(*st, stream)) return rc;
-    const size_t had = st->scan_bytes;
-    if (int rc = ensure_bytes(&st->scan_desc, &st->scan_bytes, tiles * 16, true, stream))
+    stream_workspace* ws = nullptr;
+    if (int rc = workspace_for(*st, stream, &ws)) return rc;
+    constexpr int k  = desc_io::bytes == 8 ? 0 : 1;
+    const size_t had = ws->desc_bytes[k];
+    if (int rc = ensure_bytes(&ws->desc[k], &ws->desc_bytes[k], tiles * desc_io::bytes, true, stream))
         return rc;
-    if (st->scan_bytes != had) st->scan_epoch = 0;
-    if (++st->scan_epoch >= (1u << 30)) {
-        SCLX_CUDA(cudaMemsetAsync(st->scan_desc, 0, st->scan_bytes, stream));
-        st->scan_epoch = 1;
+    if (ws->desc_bytes[k] != had) ws->epoch[k] = 0;
+    if (++ws->epoch[k] >= (1u << 30)) {
+        SCLX_CUDA(cudaMemsetAsync(ws->desc[k], 0, ws->desc_bytes[k], stream));
+        ws->epoch[k] = 1;
     }
     scan_carry_t carry{lower, n_lower};
-    auto* desc = static_cast<typename desc_io::word_t*>(st->scan_desc);
+    auto* desc = static_cast<typename desc_io::word_t*>(ws->desc[k]);
     if (aligned) {
         auto kernel = inclusive_scan_stream_kernel<T, Op, geo::vecs, geo::chunks, geo::stages,
                                                    geo::w_red, geo::w_scan, geo::lb_k>;
@@ -249,14 +263,15 @@ int launch_scan(const T* in, T* out, size_t n, const T* lower, int n_lower, T* t
         // one persistent CTA per SM (the ring takes the whole shared memory)
         const unsigned grid = unsigned(tiles < size_t(st->sm_count) ? tiles : size_t(st->sm_count));
         kernel<<<grid, scfg::threads, scfg::smem_bytes, stream>>>(
-            in, out, n, desc, st->scan_epoch, carry, total_out, st->scan_counters, op);
+            in, out, n, desc, ws->epoch[k], carry, total_out,
+            reinterpret_cast<scan_stream_counters*>(ws->ticket + 32), op);
     } else {
         inclusive_scan_kernel<T, Op, kScanThreads, kScanVecs, false>
             <<<unsigned(tiles), kScanThreads, 0, stream>>>(
-                in, out, n, desc, st->scan_epoch, carry, total_out, op);
+                in, out, n, desc, ws->epoch[k], carry, total_out, op);
     }
     SCLX_LAUNCHED();
-    return mark_use(*st, stream);
+    return 0;
 }
 
 constexpr int kReduceThreads = 256;
@@ -270,11 +285,12 @@ int launch_reduce(const T* in, size_t n, T identity, T* out, cudaStream_t stream
     constexpr int V  = vec_traits<T>::width;
     const size_t work = (n / V + kReduceThreads - 1) / kReduceThreads;
     const unsigned grid = persistent_grid(work, 8, st->sm_count);
-    if (int rc = order_after_previous(*st, stream)) return rc;
-    if (int rc = ensure_bytes(&st->partials, &st->part_bytes, size_t(grid) * sizeof(T), false,
+    stream_workspace* sw = nullptr;
+    if (int rc = workspace_for(*st, stream, &sw)) return rc;
+    if (int rc = ensure_bytes(&sw->partials, &sw->part_bytes, size_t(grid) * sizeof(T), false,
                               stream))
         return rc;
-    reduce_workspace_t ws{st->partials, st->ticket};
+    reduce_workspace_t ws{sw->partials, sw->ticket};
     if (is_aligned16(in))
         reduce_kernel<T, Op, kReduceThreads, kReduceVecs, true>
             <<<grid, kReduceThreads, 0, stream>>>(in, n, identity, out, ws, op);
@@ -282,7 +298,7 @@ int launch_reduce(const T* in, size_t n, T identity, T* out, cudaStream_t stream
         reduce_kernel<T, Op, kReduceThreads, kReduceVecs, false>
             <<<grid, kReduceThreads, 0, stream>>>(in, n, identity, out, ws, op);
     SCLX_LAUNCHED();
-    return mark_use(*st, stream);
+    return 0;
 }
 
 // geometry: profiles/r01_rld_tune.txt (16 loads in flight, 2 accumulator sets, 4 CTAs/SM)
@@ -316,11 +332,12 @@ int launch_reduce_last_dim(const T* in, size_t rows, size_t cols, T identity, T*
         if (per_band < 1) per_band = 1;
         if (grid_x > per_band) grid_x = per_band;
     }
-    if (int rc = order_after_previous(*st, stream)) return rc;
-    if (int rc = ensure_bytes(&st->partials, &st->part_bytes,
+    stream_workspace* sw = nullptr;
+    if (int rc = workspace_for(*st, stream, &sw)) return rc;
+    if (int rc = ensure_bytes(&sw->partials, &sw->part_bytes,
                               size_t(grid_x) * rows * sizeof(T), false, stream))
         return rc;
-    reduce_workspace_t ws{st->partials, st->ticket};
+    reduce_workspace_t ws{sw->partials, sw->ticket};
     const size_t smem = size_t(kRldThreads) * vw * sizeof(T);
     dim3 grid(grid_x, grid_y);
     if (vec_ok && V > 1)
@@ -330,7 +347,7 @@ int launch_reduce_last_dim(const T* in, size_t rows, size_t cols, T identity, T*
         reduce_last_dim_kernel<T, Op, kRldThreads, kRldUnroll, 1, kRldAccs>
             <<<grid, kRldThreads, smem, stream>>>(in, rows, cols, identity, out, ws, op);
     SCLX_LAUNCHED();
-    return mark_use(*st, stream);
+    return 0;
 }
 
 template<class T>

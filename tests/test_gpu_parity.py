@@ -92,6 +92,68 @@ def test_scan_multiplies_wraps(sclx, oracle):
     assert np.array_equal(d_out.to_numpy(np.uint32), oracle.inclusive_scan(a, oracle.U32, oracle.MULTIPLIES))
 
 
+def test_scan_descriptor_words_of_different_widths_never_alias(sclx):
+    """A scan of 4-byte elements leaves 8-byte {status<<32 | value} descriptor words behind, a
+    scan of 8-byte elements 16-byte {status, value} words.  If both shared one buffer, a stale
+    32-bit VALUE could be decoded as a valid status of the other layout (e.g. a running max of
+    4*e+1 reads as AGGREGATE of epoch e).  Each width has its own buffer and epoch: interleave
+    the two in both orders with values that collide with every epoch in reach."""
+    n = 60_000  # >= 6 tiles of the streaming kernel for either width
+    ones64 = np.ones(n, dtype=np.int64)
+    d64, o64 = dev(sclx, ones64), sclx.DeviceBuffer(ones64.nbytes)
+    o32 = sclx.DeviceBuffer(n * 4)
+    for e in range(1, 40):
+        for state in (1, 2):
+            v = np.full(n, 4 * e + state, dtype=np.uint32)
+            d32 = dev(sclx, v)
+            sclx.inclusive_scan(d32, o32, n, sclx.U32, sclx.MAX)
+            sclx.inclusive_scan(d64, o64, n, sclx.I64, sclx.PLUS)
+            assert np.array_equal(o32.to_numpy(np.uint32), v)
+            assert np.array_equal(o64.to_numpy(np.int64), np.arange(1, n + 1, dtype=np.int64)), (e, state)
+    # the other direction: 64-bit prefixes whose HIGH word looks like a status of the 32-bit layout
+    ones32 = np.ones(n, dtype=np.uint32)
+    d32 = dev(sclx, ones32)
+    for e in range(1, 40):
+        hi = np.int64(((e << 2) | 2) << 32)
+        v = np.zeros(n, dtype=np.int64)
+        v[0] = hi
+        d64b = dev(sclx, v)
+        sclx.inclusive_scan(d64b, o64, n, sclx.I64, sclx.PLUS)
+        sclx.inclusive_scan(d32, o32, n, sclx.U32, sclx.PLUS)
+        assert np.array_equal(o32.to_numpy(np.uint32), np.arange(1, n + 1, dtype=np.uint32)), e
+        assert np.array_equal(o64.to_numpy(np.int64), np.full(n, hi, dtype=np.int64))
+
+
+def test_two_streams_use_separate_workspaces(sclx, oracle):
+    """the C ABI takes arbitrary caller streams: scans and reductions queued on two streams at
+    once must not share tickets, partials or look-back descriptors"""
+    s = [C.c_void_p(), C.c_void_p()]
+    for h in s:
+        sclx.check(sclx.lib.sclx_b200_stream_create(C.byref(h)))
+    n, rows, cols = (1 << 20) + 11, 48, 20_001
+    a = [_scan_inputs(oracle, 2, n, seed=91 + k) for k in range(2)]
+    m = [oracle.masked_i64(rows * cols, 7 + k, 0xFFFF).astype(np.uint32) for k in range(2)]
+    d_a = [dev(sclx, x) for x in a]
+    d_m = [dev(sclx, x) for x in m]
+    d_scan = [sclx.DeviceBuffer(x.nbytes) for x in a]
+    d_row = [sclx.DeviceBuffer(rows * 4) for _ in range(2)]
+    d_tot = [sclx.DeviceBuffer(8) for _ in range(2)]
+    for _ in range(20):
+        for k in range(2):
+            sclx.inclusive_scan(d_a[k], d_scan[k], n, sclx.I64, sclx.PLUS, stream=s[k])
+            sclx.reduce_last_dim(d_m[k], rows, cols, sclx.U32, sclx.PLUS, 0, d_row[k], stream=s[k])
+            sclx.reduce(d_a[k], n, sclx.I64, sclx.PLUS, 0, d_tot[k].ptr, stream=s[k])
+    for h in s:
+        sclx.check(sclx.lib.sclx_b200_stream_synchronize(h))
+    for k in range(2):
+        assert np.array_equal(d_scan[k].to_numpy(np.int64), np.cumsum(a[k]))
+        assert np.array_equal(d_row[k].to_numpy(np.uint32, count=rows),
+                              m[k].reshape(cols, rows).sum(axis=0, dtype=np.uint64).astype(np.uint32))
+        assert int(d_tot[k].to_numpy(np.int64, count=1)[0]) == int(a[k].sum())
+    for h in s:
+        sclx.check(sclx.lib.sclx_b200_stream_destroy(h))
+
+
 @pytest.mark.parametrize("n", [0])
 def test_scan_empty(sclx, n):
     buf = sclx.DeviceBuffer(64)
