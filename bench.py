@@ -4,27 +4,39 @@
     python bench.py --gpus N --steps K --warmup W [--impl reference]
 
 Workload (BASELINE.json configs[1], the configuration the metric is quoted on):
-    sclx::algorithm::reduce_last_dim sum over float32 [64, 2^24] (4 GiB) per GPU.
-One "step" = one pass of the hot path over that array.  With N > 1 (torchrun, one rank per
-GPU) the array is [64, N*2^24] partitioned along its last dimension exactly like
-array::set_primary_devices (weak scaling: per-GPU work fixed); each step ends with the real
-exchange step of the path — an NCCL all-gather of the N partial rows (N x 256 bytes) folded
-in fixed partition order.
+    sclx::algorithm::reduce_last_dim sum over float32 [64, 2^24] (4 GiB) per GPU, i.e. ONE
+    sclx::array<float, 2>{64, N*2^24} partitioned along its last dimension over N GPUs
+    (weak scaling: per-GPU work fixed).  One "step" = one blocking public API call.
 
-value  = algorithmic bytes of all ranks / device time (CUDA events, max over ranks), inputs
-         resident in HBM.
-e2e    = the same metric through the host-buffer C-ABI call (sclx_b200_reduce_last_dim_host):
-         every step copies the 4 GiB input from pinned host memory and reads the 256-byte
-         result back, inside the timed region.
-The other BASELINE.json configs (scan, execute_kernel axpy, gather) are measured briefly at
-N=1 and reported under "also" with their own roofline fractions.
+Both arms run the SAME program through the SAME public API: drivers/parity_driver.cu, built
+against include/ (ours: drivers/bin/parity_driver_ours) and against the unmodified reference
+headers (oracle/_ref/parity_driver_ref, Unified-Memory build).  The product's execution model is
+the reference's: ONE process drives all N devices (peer-mapped VMM sclx::array, launch groups on
+persistent per-device streams), so under torchrun rank 0 runs the N-device job with
+CUDA_VISIBLE_DEVICES=0..N-1 while the other ranks wait at a barrier.
+
+value  = algorithmic bytes of the whole array / wall clock of the blocking sclx:: call (array
+         resident in device memory), the same clock on both arms.
+roofline = the dominant kernel alone (reduce_last_dim_kernel through the C ABI, CUDA events on
+         the launching stream) against the measured HBM peak.
+e2e    = the same call when every step starts with the input HOST-resident and ends with the
+         result read on the host (parity_driver bench_e2e): host->device traffic is inside
+         the clock on both arms (mirror write-back here, Unified-Memory migration there).
+also   = the other BASELINE.json configs through the same driver at this N: reduce_last_dim
+         strong-scaled, inclusive_scan with carry exchange, axpy through execute_kernel (rank 1
+         and 3), the cross-partition gather in lambda and exchange form, config 1.
+Before anything is timed, the driver's results on the N devices are checked against closed
+forms computed here with numpy (bit-exact for integer work and data movement, 1e-5 relative
+for the float sum); a mismatch aborts the run.
 """
 import argparse
 import ctypes as C
+import datetime
 import json
 import os
 import subprocess
 import sys
+import tempfile
 import threading
 import time
 
@@ -36,6 +48,9 @@ sys.path.insert(0, REPO)
 ROWS, COLS = 64, 1 << 24
 METRIC = "reduce_last_dim effective bandwidth (algorithmic bytes / time)"
 UNIT = "GB/s"
+OURS_BIN = os.path.join(REPO, "drivers", "bin", "parity_driver_ours")
+REF_BIN = os.path.join(REPO, "oracle", "_ref", "parity_driver_ref")
+NVLINK_PEAK = 900.0  # GB/s per direction per GPU (BASELINE.json north_star)
 
 
 def measured_peak():
@@ -47,20 +62,23 @@ def measured_peak():
 
 
 class ClockSampler:
-    """samples nvidia-smi clocks / throttle reasons while a timed region runs"""
+    """samples nvidia-smi clocks / throttle reasons of the first `ngpu` GPUs while a timed region runs"""
 
-    Q = ("clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
-         "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+    Q = ("index,clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
+         "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap,utilization.gpu")
 
-    def __init__(self, index):
-        self.index, self.samples, self.stop_flag, self.thread = index, [], False, None
+    def __init__(self, ngpu):
+        self.ngpu, self.samples, self.stop_flag, self.thread = ngpu, [], False, None
 
     def _run(self):
         while not self.stop_flag:
             try:
-                out = subprocess.run(["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits",
-                                      "-i", str(self.index)], capture_output=True, text=True, timeout=5).stdout
-                self.samples.append([c.strip() for c in out.strip().split(",")])
+                out = subprocess.run(["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits"],
+                                     capture_output=True, text=True, timeout=5).stdout
+                for ln in out.strip().splitlines():
+                    cells = [c.strip() for c in ln.split(",")]
+                    if cells and cells[0].isdigit() and int(cells[0]) < self.ngpu:
+                        self.samples.append(cells)
             except Exception:
                 pass
             time.sleep(0.1)
@@ -78,18 +96,26 @@ class ClockSampler:
         sm, mx, reasons = [], 0.0, set()
         names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
         for s in self.samples:
-            if len(s) < 6:
+            if len(s) < 8:
                 continue
             try:
-                sm.append(float(s[0]))
-                mx = max(mx, float(s[1]))
+                busy = float(s[7]) > 0
+                if busy:
+                    sm.append(float(s[1]))
+                mx = max(mx, float(s[2]))
             except ValueError:
                 continue
-            for name, v in zip(names, s[2:6]):
+            for name, v in zip(names, s[3:7]):
                 if v.lower().startswith("active"):
                     reasons.add(name)
+        if not sm:  # nothing sampled under load: fall back to every sample
+            for s in self.samples:
+                try:
+                    sm.append(float(s[1]))
+                except (ValueError, IndexError):
+                    pass
         return {"sm_mhz": float(np.median(sm)) if sm else None, "sm_max_mhz": mx or None,
-                "reasons": sorted(reasons), "samples": len(sm)}
+                "reasons": sorted(reasons), "samples": len(sm), "gpus": self.ngpu}
 
 
 def host_threads():
@@ -101,7 +127,7 @@ def host_threads():
 
 def cpu_baseline_hostloop(threads):
     """BASELINE.md §4.2 host loop on a bounded sample of the same workload (oracle/ is the
-    checker; this is the one leg of bench.py allowed to execute it)."""
+    checker; this is the one leg of the ours arm allowed to execute it)."""
     import oracle
 
     sample_cols = 1 << 22  # [64, 2^22] fp32 = 1 GiB
@@ -120,68 +146,141 @@ def cpu_baseline_hostloop(threads):
 
 
 # --------------------------------------------------------------------------------------------
+# the driver binary (one source, two builds)
+def driver_env(ngpu, extra=None):
+    env = dict(os.environ)
+    for k in ("SCLX_B200_EMULATE_DEVICES", "SCLX_GATHER_MODE"):
+        env.pop(k, None)
+    env["CUDA_VISIBLE_DEVICES"] = ",".join(str(i) for i in range(ngpu))
+    if extra:
+        env.update(extra)
+    return env
+
+
+def run_driver(binary, argv, ngpu, extra_env=None, timeout=1500):
+    """runs `binary argv...` on the first ngpu GPUs and returns the JSON object it prints"""
+    p = subprocess.run([binary, *[str(a) for a in argv]], capture_output=True, text=True, timeout=timeout,
+                       env=driver_env(ngpu, extra_env))
+    if p.returncode != 0:
+        raise RuntimeError(f"{os.path.basename(binary)} {' '.join(map(str, argv))}: rc={p.returncode}\n"
+                           f"{p.stdout[-1000:]}\n{p.stderr[-2000:]}")
+    for ln in p.stdout.splitlines():
+        if ln.startswith("{"):
+            return json.loads(ln)
+    raise RuntimeError(f"{os.path.basename(binary)} {' '.join(map(str, argv))}: no JSON line\n{p.stdout[-1000:]}")
+
+
+def dump_driver(binary, case, n, dtype, ngpu, extra_env=None):
+    with tempfile.TemporaryDirectory() as tmp:
+        path = os.path.join(tmp, "out.bin")
+        p = subprocess.run([binary, "dump", case, str(n), path], capture_output=True, text=True, timeout=900,
+                           env=driver_env(ngpu, extra_env))
+        if p.returncode != 0:
+            raise RuntimeError(f"{os.path.basename(binary)} dump {case}: rc={p.returncode}\n{p.stderr[-2000:]}")
+        return np.fromfile(path, dtype=dtype)
+
+
+# ---- closed forms of the driver's cases (numpy; the generator is the driver's splitmix64) ----
+def splitmix64(seed, i):
+    with np.errstate(over="ignore"):
+        z = np.uint64(seed) + (i.astype(np.uint64) + np.uint64(1)) * np.uint64(0x9E3779B97F4A7C15)
+        z = (z ^ (z >> np.uint64(30))) * np.uint64(0xBF58476D1CE4E5B9)
+        z = (z ^ (z >> np.uint64(27))) * np.uint64(0x94D049BB133111EB)
+        return z ^ (z >> np.uint64(31))
+
+
+def uniform01(seed, n):
+    return (splitmix64(seed, np.arange(n, dtype=np.uint64)) >> np.uint64(40)).astype(np.float32) * np.float32(2.0 ** -24)
+
+
+def parity_before_timing(ngpu):
+    """the driver's results on the N real devices against closed forms; raises on a mismatch"""
+    checked = []
+
+    def exact(case, n, dtype, want, env=None):
+        got = dump_driver(OURS_BIN, case, n, dtype, ngpu, env)
+        want = np.asarray(want, dtype=dtype)
+        if got.shape != want.shape or not np.array_equal(got.view(np.uint8), want.view(np.uint8)):
+            raise SystemExit(f"bench: parity check failed: {case} on {ngpu} device(s) differs from the closed form")
+        checked.append(f"{case}:{n}")
+
+    n = 40_099
+    got = dump_driver(OURS_BIN, "rld_f32", n, np.float32, ngpu).astype(np.float64)
+    want = uniform01(0x5CA11, 64 * n).reshape(n, 64).sum(axis=0, dtype=np.float64)
+    if got.shape != want.shape or not np.all(np.abs(got - want) <= 1e-5 * np.abs(want)):
+        raise SystemExit(f"bench: parity check failed: rld_f32 on {ngpu} device(s) outside the 1e-5 tolerance")
+    checked.append(f"rld_f32:{n}")
+
+    n = 1 << 20
+    exact("scan_i64", n, np.int64,
+          np.cumsum((splitmix64(0x5CA5, np.arange(n, dtype=np.uint64)) & np.uint64(0xFFFF)).astype(np.int64)))
+    n = (1 << 20) + 7
+    with np.errstate(over="ignore"):
+        start = np.uint32(0x7FFF0000) + np.arange(n, dtype=np.uint32)
+        exact("scan_i32", n, np.int32, np.cumsum(start, dtype=np.uint32).view(np.int32))
+    n = 300_007
+    src = uniform01(0xABC, 4 * n)
+    idx = (splitmix64(0x6A7, np.arange(n, dtype=np.uint64)) % np.uint64(4 * n)).astype(np.int64)
+    exact("gather_f32", n, np.float32, src[idx])
+    srcx = src + (np.arange(4 * n, dtype=np.uint64) >> np.uint64(20)).astype(np.float32)
+    exact("gather_x_f32", n, np.float32, srcx[idx], {"SCLX_GATHER_MODE": "exchange"} if ngpu > 1 else None)
+    # axpy: y = 1.5*x + y with the multiply-add contracted to one FMA on the device; the fp64
+    # evaluation rounds twice, so allow the last bit here (tests/ hold it to the C oracle's fmaf)
+    n = 1_000_003
+    x = uniform01(1, n) * np.float32(2) - np.float32(1)
+    y = uniform01(2, n) * np.float32(2) - np.float32(1)
+    got = dump_driver(OURS_BIN, "axpy_f32", n, np.float32, ngpu)
+    want = (1.5 * x.astype(np.float64) + y.astype(np.float64)).astype(np.float32)
+    if got.shape != want.shape or not np.all(np.abs(got - want) <= np.spacing(np.abs(want))):
+        raise SystemExit(f"bench: parity check failed: axpy_f32 on {ngpu} device(s)")
+    checked.append(f"axpy_f32:{n}")
+    return checked
+
+
+# --------------------------------------------------------------------------------------------
 def run_reference(args):
     """Reference arm.  Scalix has NO CPU implementation (every array is cudaMallocManaged), so
     this arm runs the UNMODIFIED reference headers through their own public API: the driver
     drivers/parity_driver.cu compiled against /root/reference (oracle/_ref/parity_driver_ref,
-    Unified-Memory build) when it was built, else the multithreaded host-loop port."""
+    Unified-Memory build) — the same program, clock and workload as our arm."""
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
         return 0
     n = args.gpus
     threads = host_threads()
-    ref_bin = os.path.join(REPO, "oracle", "_ref", "parity_driver_ref")
-    line = None
-    if os.path.exists(ref_bin):
-        env = dict(os.environ)
-        env["CUDA_VISIBLE_DEVICES"] = ",".join(str(i) for i in range(n))
-        try:
-            out = subprocess.run([ref_bin, "bench", "rld_f32", str(COLS * n), str(args.steps), str(args.warmup)],
-                                 capture_output=True, text=True, timeout=900, env=env)
-            if out.returncode != 0:
-                sys.stderr.write(f"reference UM build exited {out.returncode}: {out.stderr[-500:]}\n")
-            for ln in out.stdout.splitlines():
-                if ln.startswith("{"):
-                    r = json.loads(ln)
-                    gbs = ROWS * COLS * n * 4 / (r["ms_per_step"] * 1e-3) / 1e9
-                    line = {
-                        "metric": METRIC, "value": round(gbs, 2), "unit": UNIT, "n_gpus": n, "steps": args.steps,
-                        "warmup": args.warmup, "ms_per_step": round(r["ms_per_step"], 4), "higher_is_better": True,
-                        "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-                        "impl": "reference",
-                        "config": {"workload": f"reduce_last_dim sum f32 [64, {n}*2^24], reference Unified-Memory build "
-                                               "(sclx::algorithm::reduce_last_dim, arrays resident in managed memory)"},
-                        "cpu_baseline": {"value": round(gbs, 2), "unit": UNIT, "cores": threads, "kind": "reference",
-                                         "sample": "unmodified reference headers, UM GPU build (the reference has no CPU path)"},
-                        "e2e": {"value": round(gbs, 2), "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
-                    }
-        except Exception as exc:  # fall through to the port
-            sys.stderr.write(f"reference UM build failed: {exc}\n")
-    if line is None:
-        cb = cpu_baseline_hostloop(threads)
-        ms = (ROWS * COLS * 4 / 1e9) / cb["value"] * 1e3
-        line = {
-            "metric": METRIC, "value": cb["value"], "unit": UNIT, "n_gpus": n, "steps": args.steps,
-            "warmup": args.warmup, "ms_per_step": round(ms, 3), "higher_is_better": True, "scaling": "weak",
-            "vs_baseline": None, "dtype": "f32", "data": "synthetic", "impl": "reference",
-            "config": {"workload": "reduce_last_dim sum f32 [64, 2^24]: host-loop port on a 1 GiB sample "
-                                   "(the reference has no CPU path; its UM build was not available)"},
-            "cpu_baseline": cb,
-            "e2e": {"value": cb["value"], "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
-        }
+    if not os.path.exists(REF_BIN):
+        sys.stderr.write(f"bench.py --impl reference: {REF_BIN} is missing.  It is built from /root/reference by "
+                         "`make -C oracle ref` (run by __graft_entry__.build()); there is no substitute for it.\n")
+        print(json.dumps({"impl": "reference", "unavailable": "oracle/_ref/parity_driver_ref was not built"}), flush=True)
+        return 3
+    nbytes = ROWS * COLS * n * 4
+    r = run_driver(REF_BIN, ["bench", "rld_f32", COLS * n, args.steps, args.warmup], n)
+    gbs = nbytes / (r["ms_per_step"] * 1e-3) / 1e9
+    e2e_steps = max(1, min(args.steps, 3))
+    e2e = run_driver(REF_BIN, ["bench_e2e", "rld_f32", COLS * n, e2e_steps, 1], n, timeout=3000)
+    e2e_gbs = nbytes / (e2e["ms_per_step"] * 1e-3) / 1e9
+    line = {
+        "metric": METRIC, "value": round(gbs, 2), "unit": UNIT, "n_gpus": n, "steps": args.steps,
+        "warmup": args.warmup, "ms_per_step": round(r["ms_per_step"], 4), "higher_is_better": True,
+        "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+        "impl": "reference",
+        "config": {"workload": f"reduce_last_dim sum f32 [64, {n}*2^24] in one process on {n} GPU(s), reference "
+                               "Unified-Memory build (sclx::algorithm::reduce_last_dim; wall clock of the blocking call)",
+                   "timing": "wall clock around the blocking public API call, array resident in managed memory"},
+        "cpu_baseline": {"value": round(gbs, 2), "unit": UNIT, "cores": threads, "kind": "reference",
+                         "sample": "unmodified reference headers, UM GPU build (the reference has no CPU path)"},
+        "e2e": {"value": round(e2e_gbs, 2), "unit": UNIT, "h2d_bytes_per_step": int(e2e["h2d_bytes_per_step"]),
+                "d2h_bytes_per_step": int(e2e["d2h_bytes_per_step"]), "ms_per_step": round(e2e["ms_per_step"], 3),
+                "steps": e2e_steps,
+                "how": "parity_driver bench_e2e: input host-resident at the start of every step "
+                       "(prefetch_async({cpu}) + host memcpy outside the clock), reduce_last_dim + host read of "
+                       "the 64 results inside; the bytes migrate to the GPUs through Unified Memory"},
+    }
     print(json.dumps(line), flush=True)
     return 0
 
 
 # --------------------------------------------------------------------------------------------
-def fill_pinned_uniform(pinned, seed):
-    rng = np.random.default_rng(seed)
-    a = pinned.array
-    chunk = 1 << 24
-    for i in range(0, a.size, chunk):
-        rng.random(out=a[i:i + chunk], dtype=np.float32)
-
-
 def time_events(torch, fn, steps):
     """device time of `steps` back-to-back calls of fn() on the current stream, in ms"""
     s, e = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
@@ -193,92 +292,100 @@ def time_events(torch, fn, steps):
     return s.elapsed_time(e)
 
 
-def also_configs(sclx, torch, stream, peak):
-    """the other BASELINE.json configs at N=1, briefly (device-resident, CUDA events)"""
+def kernel_roofline(torch, sclx, steps, peak):
+    """the dominant kernel alone: reduce_last_dim_kernel over float32 [64, 2^24] through the C
+    ABI on this process's GPU, one CUDA-event pair per launch on the launching stream"""
+    stream = torch.cuda.current_stream().cuda_stream
+    nbytes = ROWS * COLS * 4
+    pinned = sclx.PinnedBuffer(ROWS * COLS, np.float32)
+    rng = np.random.default_rng(0x5CA11)
+    chunk = 1 << 24
+    for i in range(0, pinned.array.size, chunk):
+        rng.random(out=pinned.array[i:i + chunk], dtype=np.float32)
+    d_in = sclx.DeviceBuffer(nbytes)
+    sclx.check(sclx.lib.sclx_b200_memcpy_h2d(d_in.ptr, pinned.ptr, nbytes, stream))
+    row = torch.zeros(ROWS, dtype=torch.float32, device="cuda")
+    ident = np.zeros(1, np.float32)
+
+    def kernel_only():
+        sclx.check(sclx.lib.sclx_b200_reduce_last_dim(d_in.ptr, ROWS, COLS, sclx.F32, sclx.PLUS, ident.ctypes.data,
+                                                      row.data_ptr(), stream))
+
+    for _ in range(3):
+        kernel_only()
+    torch.cuda.synchronize()
+    l0 = sclx.launch_count()
+    kt = [time_events(torch, kernel_only, 1) for _ in range(steps)]
+    launches = sclx.launch_count() - l0
+    torch.cuda.synchronize()
+    got = row.cpu().numpy().astype(np.float64)
+    want = pinned.array.reshape(COLS, ROWS).sum(axis=0, dtype=np.float64)
+    if not np.all(np.abs(got - want) <= 1e-5 * np.abs(want)):
+        raise SystemExit("bench: reduce_last_dim kernel result outside the 1e-5 tolerance")
+    kernel_ms = float(np.mean(kt))
+    achieved = (nbytes + ROWS * 4) / (kernel_ms * 1e-3) / 1e9
+    h2d_ms = time_events(torch, lambda: sclx.check(
+        sclx.lib.sclx_b200_memcpy_h2d(d_in.ptr, pinned.ptr, nbytes, stream)), 2) / 2
+    pinned.free()
+    del d_in
+    roof = {"bound": "hbm", "achieved": round(achieved, 1), "peak": peak, "unit": "GB/s",
+            "frac": round(achieved / peak, 4), "traffic": None,
+            "kernel": "reduce_last_dim_kernel<float, op_plus, 256, 16, 4, 2>", "kernel_ms": round(kernel_ms, 4),
+            "how": "C-ABI launch on torch's current stream, one CUDA-event pair per launch, input 4 GiB (> L2)"}
+    traffic_file = os.path.join(REPO, "profiles", "traffic.json")
+    if os.path.exists(traffic_file):
+        try:
+            roof["traffic"] = json.load(open(traffic_file)).get("reduce_last_dim_bytes_per_launch")
+        except Exception:
+            pass
+    return roof, int(launches), nbytes / (h2d_ms * 1e-3) / 1e9
+
+
+def also_lines(n, peak, steps, warmup):
+    """the other BASELINE.json configs through the same driver on the same N devices"""
     out = {}
 
-    def entry(name, nbytes, fn, reps=10, warm=3, note=None):
-        for _ in range(warm):
-            fn()
-        torch.cuda.synchronize()
-        ms = time_events(torch, fn, reps) / reps
-        gbs = nbytes / (ms * 1e-3) / 1e9
-        out[name] = {"GB/s": round(gbs, 1), "ms": round(ms, 4), "frac_of_measured_hbm": round(gbs / peak, 3)}
+    def line(name, case, size, alg_bytes, env=None, note=None, k=None, nvlink_bytes=None):
+        try:
+            r = run_driver(OURS_BIN, ["bench", case, size, k or steps, warmup], n, env)
+        except Exception as exc:  # one failing side line must not lose the headline
+            out[name] = {"error": str(exc)[-400:]}
+            return
+        ms = r["ms_per_step"]
+        gbs = alg_bytes / (ms * 1e-3) / 1e9
+        e = {"ms": round(ms, 4), "GB/s": round(gbs, 1), "GB/s_per_gpu": round(gbs / n, 1),
+             "frac_of_measured_hbm_per_gpu": round(gbs / n / peak, 3)}
+        if r.get("device_ms_per_step") is not None:
+            e["device_ms"] = round(r["device_ms_per_step"], 4)
+        if nvlink_bytes is not None and n > 1:
+            e["nvlink_payload_GB/s_per_gpu"] = round(nvlink_bytes / n / (ms * 1e-3) / 1e9, 1)
+            e["frac_of_nvlink_per_gpu"] = round(nvlink_bytes / n / (ms * 1e-3) / 1e9 / NVLINK_PEAK, 4)
         if note:
-            out[name]["note"] = note
+            e["note"] = note
+        out[name] = e
 
-    flush = sclx.DeviceBuffer(256 << 20)
-
-    def with_flush(fn):
-        # 2^24-element arrays fit in the 126 MB L2: evict them between iterations
-        def g():
-            sclx.fill(flush, (256 << 20) // 4, 1, np.uint32, stream=stream)
-            fn()
-        return g
-
-    # config 1: iota + inclusive_scan over 2^24 int32
-    n1 = 1 << 24
-    a1, o1 = sclx.DeviceBuffer(n1 * 4), sclx.DeviceBuffer(n1 * 4)
-    sclx.iota(a1, n1, sclx.I32, 0, stream=stream)
-    scan1 = lambda: sclx.inclusive_scan(a1, o1, n1, sclx.I32, sclx.PLUS, stream=stream)
-    for _ in range(3):
-        scan1()
-    torch.cuda.synchronize()
-    # time the scan alone with an L2 flush before each (events around the scan only)
-    times = []
-    for _ in range(10):
-        sclx.fill(flush, (256 << 20) // 4, 1, np.uint32, stream=stream)
-        s, e = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-        s.record(); scan1(); e.record(); e.synchronize()
-        times.append(s.elapsed_time(e))
-    ms = float(np.median(times))
-    out["config1_scan_i32_2^24"] = {"GB/s": round(n1 * 8 / (ms * 1e-3) / 1e9, 1), "ms": round(ms, 4),
-                                    "frac_of_measured_hbm": round(n1 * 8 / (ms * 1e-3) / 1e9 / peak, 3),
-                                    "note": "128 MiB algorithmic, L2 flushed before each launch; launch-latency bound"}
-    del a1, o1
-
-    # config 5 (per-GPU share at 8 GPUs): inclusive_scan over 2^29 int64 with a carry-in
-    n5 = 1 << 29
-    a5, o5 = sclx.DeviceBuffer(n5 * 8), sclx.DeviceBuffer(n5 * 8)
-    tot = sclx.DeviceBuffer(64)
-    sclx.iota(a5, n5, sclx.I64, 0, stream=stream)
-    entry("config5_scan_i64_2^29_per_gpu_share",
-          n5 * 16, lambda: sclx.inclusive_scan(a5, o5, n5, sclx.I64, sclx.PLUS, lower_totals=tot.ptr, n_lower=1,
-                                               stream=stream), reps=5)
-    entry("config5_reduce_pass_i64_2^29", n5 * 8,
-          lambda: sclx.reduce(a5, n5, sclx.I64, sclx.PLUS, 0, tot.ptr, stream=stream), reps=5,
-          note="pass A (per-partition total) of the multi-device scan")
-    del a5, o5
-
-    # config 3: axpy through the execute_kernel range dispatcher over 2^30 f32
-    n3 = 1 << 30
-    x3, y3 = sclx.DeviceBuffer(n3 * 4), sclx.DeviceBuffer(n3 * 4)
-    sclx.fill(x3, n3, 0.5, np.float32, stream=stream)
-    entry("config3_axpy_dispatch_f32_2^30", n3 * 12,
-          lambda: sclx.axpy_f32(1.0, x3.ptr, y3.ptr, n3, 1, stream=stream), reps=5)
-    entry("fill_f32_2^30", n3 * 4, lambda: sclx.fill(y3, n3, 1.0, np.float32, stream=stream), reps=5)
-
-    # config 4 on one GPU: 2^28 random u64 indices into the 2^30-float array
-    n4 = 1 << 28
-    idx_host = np.random.default_rng(0x6A7).integers(0, n3, size=1 << 24, dtype=np.uint64)
-    i4, o4 = sclx.DeviceBuffer(n4 * 8), sclx.DeviceBuffer(n4 * 4)
-    for b in range(n4 // idx_host.size):  # replicate a 2^24-index block with a rotating offset
-        blk = (idx_host + np.uint64(b * 7919)) % np.uint64(n3)
-        sclx.check(sclx.lib.sclx_b200_memcpy_h2d(i4.ptr + b * blk.nbytes, blk.ctypes.data, blk.nbytes, None))
-        sclx.synchronize()
-    entry("config4_gather_kernel_2^28_into_2^30", n4 * 16,
-          lambda: sclx.gather(i4.ptr, n4, 8, [x3], 0, 4, o4.ptr, stream=stream), reps=3,
-          note="16 B/gather algorithmic (idx 8 + out 4 + payload 4); HBM moves a 32 B sector per payload")
-    entry("config4_gather_via_range_launch", n4 * 16,
-          lambda: sclx.gather_launch_f32(i4.ptr, n4, x3.ptr, o4.ptr, 1, stream=stream), reps=3)
+    g = 1 << 28
+    line("config2_rld_f32_strong_[64,2^24]_total", "rld_f32", COLS, ROWS * COLS * 4,
+         note="BASELINE config 2 as ONE [64, 2^24] array sharded over the N devices (strong scaling)")
+    line("config5_scan_i64_N*2^29", "scan_i64", n << 29, (n << 29) * 16,
+         note="inclusive_scan over N*2^29 int64 with cross-device carry (2^32 at N=8); 16 B/element algorithmic", k=5)
+    line("config3_axpy_f32_2^30_strong", "axpy_f32", 1 << 30, (1 << 30) * 12,
+         note="user lambda y = a*x + y through execute_kernel, 2^30 elements in total", k=5)
+    line("config3_axpy_f32_rank3_{4,4,2^26}", "axpy_f32_r3", 1 << 30, (1 << 30) * 12, k=5)
+    remote = (n - 1) / n
+    line("config4_gather_lambda_2^28_into_2^30", "gather_f32", g, g * 16, k=3,
+         note="out[i] = src[index[i]] as a user lambda: cross-partition reads are NVLink peer loads",
+         nvlink_bytes=g * 4 * remote)
+    line("config4_gather_algorithm_2^28_into_2^30", "gather_x_f32", g, g * 16, k=3,
+         note="sclx::algorithm::gather (binned / exchange form)", nvlink_bytes=g * 4 * remote)
+    line("config1_scan_i32_2^24", "scan_i32", 1 << 24, (1 << 24) * 8, k=20,
+         note="128 MiB algorithmic: launch-latency bound; arrays stay L2-resident between iterations")
     return out
 
 
 def run_ours(args):
     import torch
     import torch.distributed as dist
-
-    import scalix_b200 as sclx
 
     n = args.gpus
     rank = int(os.environ.get("RANK", "0"))
@@ -287,151 +394,85 @@ def run_ours(args):
     if n > 1 and world != n:
         raise SystemExit(f"--gpus {n} needs torchrun with {n} ranks (WORLD_SIZE={world})")
     torch.cuda.set_device(local_rank)
-    sclx.check(sclx.lib.sclx_b200_set_device(local_rank))
+    host_group = None
     if world > 1:
         dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
-    stream = torch.cuda.current_stream().cuda_stream
-    peak, peak_kind = measured_peak()
-    nbytes = ROWS * COLS * 4
+        # the waiting ranks must not spin on their GPUs: they wait on a host-side (gloo) barrier
+        host_group = dist.new_group(backend="gloo", timeout=datetime.timedelta(hours=3))
+        dist.barrier()
+        torch.cuda.synchronize()
+    warmup = max(args.warmup, 3)
 
-    # ---- synthetic input: this rank's partition, generated in pinned host memory ----------
-    pinned = sclx.PinnedBuffer(ROWS * COLS, np.float32)
-    fill_pinned_uniform(pinned, 0x5CA11 + rank)
-    d_in = sclx.DeviceBuffer(nbytes)
-    sclx.check(sclx.lib.sclx_b200_memcpy_h2d(d_in.ptr, pinned.ptr, nbytes, stream))
-    row = torch.zeros(ROWS, dtype=torch.float32, device="cuda")
-    gathered = torch.zeros(world * ROWS, dtype=torch.float32, device="cuda")
-    result = torch.zeros(ROWS, dtype=torch.float32, device="cuda")
-    ident = np.zeros(1, np.float32)
-
-    def kernel_only():
-        sclx.check(sclx.lib.sclx_b200_reduce_last_dim(d_in.ptr, ROWS, COLS, sclx.F32, sclx.PLUS, ident.ctypes.data,
-                                                      row.data_ptr(), stream))
-
-    def exchange():
-        if world > 1:
-            dist.all_gather_into_tensor(gathered, row)
-            sclx.check(sclx.lib.sclx_b200_fold_rows(gathered.data_ptr(), world, ROWS, sclx.F32, sclx.PLUS,
-                                                    ident.ctypes.data, result.data_ptr(), stream))
-
-    def step():
-        kernel_only()
-        exchange()
-
-    def barrier():
+    def host_barrier():
         torch.cuda.synchronize()
         if world > 1:
-            dist.barrier()
-            torch.cuda.synchronize()
-
-    launches0 = sclx.launch_count()
-    for _ in range(max(args.warmup, 3)):
-        step()
-    barrier()
-
-    # ---- value: K steps, device time, max over ranks ------------------------------------------
-    # the sampler stays on through both timed regions (value and e2e): K device-resident
-    # steps last ~12 ms, too short for more than one nvidia-smi sample on their own
-    clocks = ClockSampler(local_rank)
-    clocks.__enter__()
-    barrier()
-    l_before = sclx.launch_count()
-    total_ms = time_events(torch, step, args.steps)
-    barrier()
-    gpu_launches = sclx.launch_count() - l_before
-    # dominant kernel alone: one event pair per launch
-    kt = []
-    for _ in range(args.steps):
-        kt.append(time_events(torch, kernel_only, 1))
-    torch.cuda.synchronize()
-    t = torch.tensor([total_ms], dtype=torch.float64, device="cuda")
-    if world > 1:
-        dist.all_reduce(t, op=dist.ReduceOp.MAX)
-    total_ms = float(t.item())
-    ms_per_step = total_ms / args.steps
-    value = world * nbytes / (ms_per_step * 1e-3) / 1e9
-    kernel_ms = float(np.mean(kt))
-    achieved = (nbytes + ROWS * 4) / (kernel_ms * 1e-3) / 1e9
-
-    # correctness of what was timed: fp64 check of this rank's row against numpy
-    local = row.cpu().numpy().astype(np.float64)
-    want = pinned.array.reshape(COLS, ROWS).sum(axis=0, dtype=np.float64)
-    if not np.all(np.abs(local - want) <= 1e-5 * np.abs(want)):
-        raise SystemExit("bench: reduce_last_dim result outside the 1e-5 tolerance")
-
-    # ---- e2e: host buffers through the C ABI, copies inside the timed region --------------------
-    host_out = np.zeros(ROWS, np.float32)
-    h_row = torch.zeros(ROWS, dtype=torch.float32).pin_memory()
-
-    def e2e_step():
-        sclx.reduce_last_dim_host(pinned.array, ROWS, COLS, sclx.F32, sclx.PLUS, 0.0, host_out)
-        if world > 1:
-            h_row.copy_(torch.from_numpy(host_out))
-            row.copy_(h_row, non_blocking=True)
-            exchange()
-            h_row.copy_(result)  # blocking D2H of the folded row
-
-    e2e_steps = args.steps
-    for _ in range(2):
-        e2e_step()
-    barrier()
-    t0 = time.perf_counter()
-    for _ in range(e2e_steps):
-        e2e_step()
-    torch.cuda.synchronize()
-    e2e_s = time.perf_counter() - t0
-    clocks.__exit__()
-    t = torch.tensor([e2e_s], dtype=torch.float64, device="cuda")
-    if world > 1:
-        dist.all_reduce(t, op=dist.ReduceOp.MAX)
-    e2e_s = float(t.item())
-    e2e_value = world * nbytes * e2e_steps / e2e_s / 1e9
-    if not np.all(np.abs(host_out.astype(np.float64) - want) <= 1e-5 * np.abs(want)) and world == 1:
-        raise SystemExit("bench: e2e result outside the 1e-5 tolerance")
-
-    # the bound of the host-buffer path: one plain pinned -> device copy of the same 4 GiB
-    def h2d_copy():
-        sclx.check(sclx.lib.sclx_b200_memcpy_h2d(d_in.ptr, pinned.ptr, nbytes, stream))
-
-    h2d_copy()
-    torch.cuda.synchronize()
-    h2d_peak = nbytes / (time_events(torch, h2d_copy, 2) / 2 * 1e-3) / 1e9
+            dist.barrier(group=host_group)
 
     line = None
     if rank == 0:
+        import scalix_b200 as sclx  # loads libscalix_b200.so (fails loudly if it is missing)
+
+        if not os.path.exists(OURS_BIN):
+            raise SystemExit(f"{OURS_BIN} is missing: run `python -c 'import __graft_entry__ as g; g.build()'`")
+        sclx.check(sclx.lib.sclx_b200_set_device(local_rank))
+        peak, peak_kind = measured_peak()
+        nbytes = ROWS * COLS * 4 * n
+
+        checked = parity_before_timing(n)
+
+        with ClockSampler(n) as clocks:
+            # ---- value: K blocking public-API calls on the N devices, one process ------------
+            r = run_driver(OURS_BIN, ["bench", "rld_f32", COLS * n, args.steps, warmup], n)
+            ms_per_step = r["ms_per_step"]
+            value = nbytes / (ms_per_step * 1e-3) / 1e9
+            # ---- the dominant kernel against its roofline --------------------------------------
+            roof, abi_launches, h2d_peak = kernel_roofline(torch, sclx, args.steps, peak)
+            roof["api_device_ms_per_step"] = None if r.get("device_ms_per_step") is None else round(
+                r["device_ms_per_step"], 4)
+            # ---- e2e: host-resident input, result read on the host ------------------------------
+            e2e_steps = max(1, min(args.steps, 5))
+            e2e_cols, e2e_note = COLS * n, None
+            try:
+                e = run_driver(OURS_BIN, ["bench_e2e", "rld_f32", e2e_cols, e2e_steps, 1], n)
+            except RuntimeError as exc:  # e.g. not enough pinnable host memory for N*8 GiB
+                e2e_cols //= 2
+                e2e_note = f"full size failed ({str(exc)[-120:]}); measured on half the columns"
+                e = run_driver(OURS_BIN, ["bench_e2e", "rld_f32", e2e_cols, e2e_steps, 1], n)
+            e2e_value = ROWS * e2e_cols * 4 / (e["ms_per_step"] * 1e-3) / 1e9
         line = {
             "metric": METRIC, "value": round(value, 1), "unit": UNIT, "n_gpus": n, "steps": args.steps,
-            "warmup": max(args.warmup, 3), "ms_per_step": round(ms_per_step, 4), "higher_is_better": True,
+            "warmup": warmup, "ms_per_step": round(ms_per_step, 4), "higher_is_better": True,
             "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
             "config": {
-                "workload": f"reduce_last_dim sum, float32 [64, 2^24] per GPU (global [64, {n}*2^24], last dim "
-                            "partitioned like set_primary_devices); N>1 adds an NCCL all-gather of N x 256 B + fixed-order fold",
+                "workload": f"reduce_last_dim sum, float32 [64, 2^24] per GPU: one sclx::array<float,2>{{64, {n}*2^24}} "
+                            f"partitioned over {n} GPU(s), driven by ONE process through the public sclx:: API "
+                            "(drivers/parity_driver.cu, the program the reference arm runs)",
+                "timing": "wall clock around the blocking sclx::algorithm::reduce_last_dim call, array resident in HBM; "
+                          "roofline.kernel_ms is the CUDA-event time of the kernel alone",
                 "l2": "input (4 GiB per GPU) is larger than the 126 MB L2; no flush needed",
                 "peak": f"{peak} GB/s ({peak_kind} HBM copy bandwidth)",
+                "parity_before_timing": checked,
             },
-            "roofline": {"bound": "hbm", "achieved": round(achieved, 1), "peak": peak, "unit": "GB/s",
-                         "frac": round(achieved / peak, 4), "traffic": None,
-                         "kernel": "reduce_last_dim_kernel<float, op_plus, 256, 16, 4, 2>",
-                         "kernel_ms": round(kernel_ms, 4)},
-            "e2e": {"value": round(e2e_value, 2), "unit": UNIT, "h2d_bytes_per_step": nbytes,
-                    "d2h_bytes_per_step": ROWS * 4, "ms_per_step": round(e2e_s / e2e_steps * 1e3, 3),
-                    "bound": "pcie h2d", "h2d_copy_gbs_per_gpu": round(h2d_peak, 2),
-                    "frac_of_h2d_copy": round(e2e_value / world / h2d_peak, 4)},
-            "gpu_launches": int(gpu_launches),
+            "roofline": roof,
+            "e2e": {"value": round(e2e_value, 2), "unit": UNIT, "h2d_bytes_per_step": int(e["h2d_bytes_per_step"]),
+                    "d2h_bytes_per_step": int(e["d2h_bytes_per_step"]), "ms_per_step": round(e["ms_per_step"], 3),
+                    "steps": e2e_steps, "bound": "pcie h2d", "h2d_copy_gbs_per_gpu": round(h2d_peak, 2),
+                    "frac_of_h2d_copy": round(e2e_value / n / h2d_peak, 4),
+                    "how": "parity_driver bench_e2e: input host-resident at the start of every step "
+                           "(prefetch_async({cpu}) + host memcpy outside the clock), reduce_last_dim + host read of "
+                           "the 64 results inside; the mirror's pinned pages go to their owners' GPUs in parallel"},
+            "gpu_launches": int(r.get("launches") or 0),
             "clocks": clocks.summary(),
         }
-        traffic_file = os.path.join(REPO, "profiles", "traffic.json")
-        if os.path.exists(traffic_file):
-            try:
-                line["roofline"]["traffic"] = json.load(open(traffic_file)).get("reduce_last_dim_bytes_per_launch")
-            except Exception:
-                pass
-    if n == 1:
-        pinned.free()
-        line["also"] = also_configs(sclx, torch, stream, peak)
-        line["cpu_baseline"] = cpu_baseline_hostloop(host_threads())
+        if e2e_note:
+            line["e2e"]["note"] = e2e_note
+        line["gpu_launches_note"] = (f"{line['gpu_launches']} = kernels queued by the {args.steps} timed API calls on "
+                                     f"{n} device(s); the roofline loop launched {abi_launches} more through the C ABI")
+        line["also"] = also_lines(n, peak, max(3, min(args.steps, 10)), 2)
+        if n == 1:
+            line["cpu_baseline"] = cpu_baseline_hostloop(host_threads())
+    host_barrier()
     if world > 1:
-        dist.barrier()
         dist.destroy_process_group()
     if rank == 0:
         print(json.dumps(line), flush=True)

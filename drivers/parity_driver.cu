@@ -399,6 +399,41 @@ int run_case(const std::string& what, const std::string& name, size_t n, const c
         step();
         return do_dump ? dump(out, path) : bench(step, steps, warmup);
     }
+    if (name == "gather_x_selfcheck") {
+        // config 4 at any size without a host copy of the result: the framework-owned gather
+        // (binned form) against the user-lambda gather on the device; output = {mismatches, n}
+#ifdef DRIVER_HAS_GATHER
+        sclx::array<float, 1> src({4 * n}), out({n}), want({n});
+        sclx::array<size_t, 1> index({n});
+        const size_t m = 4 * n;
+        generate(src, [] __device__(size_t i) { return uniform01(0xABC, i) + float(i >> 20); });
+        generate(index, [=] __device__(size_t i) { return size_t(splitmix64(0x6A7, i) % m); });
+        sclx::algorithm::gather(src, index, out, sclx::algorithm::gather_mode::exchange);
+        sclx::execute_kernel([&](sclx::kernel_handler& handler) {
+            handler.launch(
+                sclx::md_range_t<1>{want.shape()},
+                want,
+                [=] __device__(const sclx::md_index_t<1>& idx, const auto&) { want[idx] = src[index[idx]]; }
+            );
+        }).get();
+        sclx::array<unsigned long long, 1> differs({n});
+        sclx::execute_kernel([&](sclx::kernel_handler& handler) {
+            handler.launch(
+                sclx::md_range_t<1>{differs.shape()},
+                differs,
+                [=] __device__(const sclx::md_index_t<1>& idx, const auto&) {
+                    differs[idx] = __float_as_uint(out[idx]) != __float_as_uint(want[idx]);
+                }
+            );
+        }).get();
+        const unsigned long long bad = sclx::algorithm::reduce(differs, 0ull, sclx::algorithm::plus<>());
+        std::vector<unsigned long long> res{bad, (unsigned long long)n};
+        if (!do_dump) return 2;
+        return write_file(path, res.data(), res.size() * sizeof(unsigned long long));
+#else
+        return 2;
+#endif
+    }
     if (name == "gather_x_skew") return gather_x<float>(do_dump, n, path, steps, warmup, true);
     if (name == "gather_x_f32" || name == "gather_x_f64") {
         // configs[3] through the framework-owned gather (exchange form across partitions); the

@@ -20,6 +20,25 @@ template<class F, int U> __global__ void persistent_unrolled(F f, size_t n) {
     }
     for (; i < n; i += stride) f(i);
 }
+// verdict r01 #6(b): the dispatcher knows the RESULT array of a launch; does pulling the next
+// trip's result element into L2 ahead of time help an aliasing lambda?
+template<class F> __global__ void persistent_prefetch_result(F f, size_t n, const float* result) {
+    size_t i = size_t(blockIdx.x) * blockDim.x + threadIdx.x, stride = size_t(gridDim.x) * blockDim.x;
+    for (; i < n; i += stride) {
+        if (i + stride < n) asm volatile("prefetch.global.L2 [%0];" ::"l"(result + i + stride));
+        f(i);
+    }
+}
+template<class F> __global__ void persistent_prefetch_both(F f, size_t n, const float* a, const float* b) {
+    size_t i = size_t(blockIdx.x) * blockDim.x + threadIdx.x, stride = size_t(gridDim.x) * blockDim.x;
+    for (; i < n; i += stride) {
+        if (i + stride < n) {
+            asm volatile("prefetch.global.L2 [%0];" ::"l"(a + i + stride));
+            asm volatile("prefetch.global.L2 [%0];" ::"l"(b + i + stride));
+        }
+        f(i);
+    }
+}
 template<class F> __global__ void one_per_thread(F f, size_t n) {
     size_t i = size_t(blockIdx.x) * blockDim.x + threadIdx.x;
     if (i < n) f(i);
@@ -79,6 +98,10 @@ int main() {
         char name[96]; snprintf(name, sizeof name, "persistent block=256 grid=%dx", mult);
         timeit(name, n, [&] { persistent<<<sms * 8 * mult, 256>>>(f, n); });
     }
+    timeit("persistent 64x + L2 prefetch of result y", n, [&] { persistent_prefetch_result<<<sms * 8 * 64, 256>>>(f, n, y); });
+    timeit("persistent 1x + L2 prefetch of result y", n, [&] { persistent_prefetch_result<<<sms * 8, 256>>>(f, n, y); });
+    timeit("persistent 64x + L2 prefetch of x and y", n, [&] { persistent_prefetch_both<<<sms * 8 * 64, 256>>>(f, n, x, y); });
+    timeit("persistent 1x + L2 prefetch of x and y", n, [&] { persistent_prefetch_both<<<sms * 8, 256>>>(f, n, x, y); });
     timeit("one_per_thread block=256", n, [&] { one_per_thread<<<unsigned((n + 255) / 256), 256>>>(f, n); });
     timeit("one_per_thread block=1024", n, [&] { one_per_thread<<<unsigned((n + 1023) / 1024), 1024>>>(f, n); });
     timeit("unrolled x4 (aliasing, expect same)", n, [&] { persistent_unrolled<axpy_t, 4><<<sms * 8, 256>>>(f, n); });

@@ -4,13 +4,14 @@
 // over the range launcher (/root/reference examples/distributed_indexing.cu:146-154,
 // examples/scaling_performance.cu:59-78) and Unified Memory faults the remote pages in.  That
 // idiom keeps working here unchanged (cross-partition reads are NVLink peer loads on the
-// array's peer-mapped range), but one peer load per index is capped by NVLink's request rate
-// (detail/b200/gather_exchange.cuh).  This entry point is the framework-owned form of the same
-// operation: `index` holds linear (storage-order) indices into `src`; `out` and `index` have
-// the same length; result bits are those of the lambda form.
+// array's peer-mapped range), but one load per index is capped by NVLink's request rate across
+// GPUs and by HBM's random-access rate on one (detail/b200/gather_exchange.cuh).  This entry
+// point is the framework-owned form of the same operation: `index` holds linear (storage-order)
+// indices into `src`; `out` and `index` have the same length; result bits are those of the
+// lambda form.
 //
-//   1 source partition, or shapes the exchange does not cover -> direct kernel (peer loads)
-//   otherwise                                                  -> exchange form (K1/K2/K3)
+//   small problems, sources that fit L2, shapes the binning does not cover -> direct kernel
+//   otherwise -> binned exchange (K1 partition / K2 serve from L2-resident regions / K3 place)
 //
 // Blocking, like the reference's algorithms.
 #pragma once
@@ -18,12 +19,16 @@
 #include "../detail/b200/host_launch.cuh"
 #include "../execute_kernel.cuh"
 
+#include <algorithm>
 #include <cstdlib>
+#include <mutex>
 #include <type_traits>
 #include <vector>
 
 namespace sclx::algorithm {
 
+// `exchange` = the binned form (also on one device, where the "exchange" is between L2-sized
+// regions of the same partition)
 enum class gather_mode { automatic, direct, exchange };
 
 namespace detail {
@@ -41,16 +46,26 @@ struct gather_carrier<8> {
 
 inline size_t gx_align(size_t v) { return (v + 255) & ~size_t(255); }
 
-inline unsigned gx_capacity(size_t n_requester, int nowners) {
+inline unsigned gx_capacity(size_t n_requester, unsigned buckets) {
     // 1.25 x the uniform share + one tile (never more than the requester's whole partition),
-    // plus the padding of every tile's run to a multiple of 32 entries
-    const size_t share = (n_requester + nowners - 1) / nowners;
+    // plus the expected padding of every tile's run to a multiple of kGxRunAlign entries
+    const size_t share = (n_requester + buckets - 1) / buckets;
     size_t cap         = share + share / 4 + b200::kGxTile;
     if (cap > n_requester) cap = n_requester;
     const size_t tiles = (n_requester + b200::kGxTile - 1) / b200::kGxTile;
-    cap += tiles * 32;
+    cap += tiles * b200::kGxRunAlign;
     cap = (cap + 31) & ~size_t(31);
     return unsigned(cap);
+}
+
+// bytes of one source region: two of them (the one being served and the one being prefetched)
+// plus the streaming queues have to live in the 126 MB L2 together
+inline size_t gx_region_bytes() {
+    if (const char* e = std::getenv("SCLX_B200_GATHER_REGION_KB")) {
+        const long kb = std::atol(e);
+        if (kb > 0) return size_t(kb) << 10;
+    }
+    return size_t(32) << 20;
 }
 
 }  // namespace detail
@@ -80,7 +95,7 @@ __host__ void gather(
     using index_t_          = std::remove_const_t<I>;
     const index_t_* idx_ptr = index.data().get();
 
-    bool exchange_ok = (sizeof(T) == 4 || sizeof(T) == 8) && nown > 1 && nown <= b200::kGxMaxParts
+    bool exchange_ok = (sizeof(T) == 4 || sizeof(T) == 8) && nown >= 1 && nown <= b200::kGxMaxParts
                        && nreq <= b200::kGxMaxParts && n < (size_t(1) << 31) * size_t(nreq);
     // owners must be uniform blocks of `per` elements starting at p*per (true for every
     // array partitioned by set_primary_devices; not for arbitrary slices), distinct devices
@@ -99,12 +114,27 @@ __host__ void gather(
     }
     if (mode == gather_mode::exchange && !exchange_ok)
         throw_exception<std::invalid_argument>(
-            "exchange gather needs 4- or 8-byte elements and a source partitioned in uniform blocks over "
-            "2..16 distinct devices",
+            "binned gather needs 4- or 8-byte elements and a source partitioned in uniform blocks over "
+            "1..16 distinct devices",
             "sclx::algorithm::"
         );
+    // bucket geometry: regions of 2^shift elements inside every owner's partition
+    unsigned region_shift = 0, regions = 1;
+    if (exchange_ok) {
+        size_t region_elems = detail::gx_region_bytes() / sizeof(T);
+        while ((size_t(1) << (region_shift + 1)) <= region_elems) ++region_shift;
+        regions = unsigned((per + (size_t(1) << region_shift) - 1) >> region_shift);
+        while (size_t(regions) * size_t(nown) > size_t(b200::kGxMaxBuckets) / 2) {  // <= 256 buckets: runs of >= 16
+            ++region_shift;
+            regions = unsigned((per + (size_t(1) << region_shift) - 1) >> region_shift);
+        }
+    }
+    // worth it when requests cross devices, or when the source is too large for L2 to absorb
+    // the random reads by itself
+    const bool pays = nown > 1 || src.elements() * sizeof(T) > (size_t(96) << 20);
     const bool use_exchange
-        = exchange_ok && (mode == gather_mode::exchange || (mode == gather_mode::automatic && n >= (size_t(1) << 18)));
+        = exchange_ok
+       && (mode == gather_mode::exchange || (mode == gather_mode::automatic && pays && n >= (size_t(1) << 18)));
 
     if constexpr (sizeof(T) != 4 && sizeof(T) != 8) {
         // direct kernel on raw element type
@@ -131,13 +161,17 @@ __host__ void gather(
                     );
             });
         } else {
+            // the per-device exchange workspace is shared: one binned gather at a time
+            static std::mutex workspace_mutex;
+            std::lock_guard<std::mutex> workspace_lock(workspace_mutex);
+            const unsigned buckets = regions * unsigned(nown);
             // ---- workspace layout, per logical device ------------------------------------
             std::vector<size_t> n_r(nreq), tiles_r(nreq);
-            std::vector<std::vector<unsigned>> cap(nreq, std::vector<unsigned>(nown));
+            std::vector<unsigned> cap(nreq);
             for (int r = 0; r < nreq; ++r) {
                 n_r[r]     = std::get<2>(out_info[r]);
                 tiles_r[r] = (n_r[r] + b200::kGxTile - 1) / b200::kGxTile;
-                for (int q = 0; q < nown; ++q) cap[r][q] = n_r[r] ? detail::gx_capacity(n_r[r], nown) : 0;
+                cap[r]     = n_r[r] ? detail::gx_capacity(n_r[r], buckets) : 0;
             }
             struct dev_layout {
                 int device;
@@ -163,13 +197,13 @@ __host__ void gather(
             std::vector<size_t> counters_off(nreq), pos_off(nreq), tbase_off(nreq), tcnt_off(nreq);
             for (int r = 0; r < nreq; ++r) {
                 const int rdev  = std::get<0>(out_info[r]);
-                counters_off[r] = reserve(rdev, sizeof(unsigned) * b200::kGxMaxParts);
+                counters_off[r] = reserve(rdev, sizeof(unsigned) * buckets);
                 pos_off[r]      = reserve(rdev, tiles_r[r] * b200::kGxTile * sizeof(unsigned short));
-                tbase_off[r]    = reserve(rdev, tiles_r[r] * nown * sizeof(unsigned));
-                tcnt_off[r]     = reserve(rdev, tiles_r[r] * nown * sizeof(unsigned short));
+                tbase_off[r]    = reserve(rdev, tiles_r[r] * buckets * sizeof(unsigned));
+                tcnt_off[r]     = reserve(rdev, tiles_r[r] * buckets * sizeof(unsigned short));
                 for (int q = 0; q < nown; ++q) {
-                    resp_off[r][q]  = reserve(rdev, size_t(cap[r][q]) * sizeof(U));
-                    queue_off[r][q] = reserve(std::get<0>(src_info[q]), size_t(cap[r][q]) * sizeof(unsigned));
+                    resp_off[r][q]  = reserve(rdev, size_t(regions) * cap[r] * sizeof(U));
+                    queue_off[r][q] = reserve(std::get<0>(src_info[q]), size_t(regions) * cap[r] * sizeof(unsigned));
                 }
             }
             for (auto& d : devs) {
@@ -179,7 +213,11 @@ __host__ void gather(
             }
             auto at = [&](int device, size_t off) { return dev_slot(device).base + off; };
 
-            const b200::gx_div_t div = b200::gx_make_div(per);
+            b200::gx_geometry_t geo;
+            geo.div          = b200::gx_make_div(per);
+            geo.region_shift = region_shift;
+            geo.regions      = regions;
+            geo.buckets      = buckets;
             std::vector<b200::gx_requester_t<U>> rq(nreq);
             for (int r = 0; r < nreq; ++r) {
                 const int rdev = std::get<0>(out_info[r]);
@@ -188,61 +226,72 @@ __host__ void gather(
                 x.src_base     = src_base;
                 x.n            = n_r[r];
                 x.nowners      = nown;
-                x.div          = div;
+                x.geo          = geo;
+                x.cap          = cap[r];
                 x.counters     = reinterpret_cast<unsigned*>(at(rdev, counters_off[r]));
                 x.pos          = reinterpret_cast<unsigned short*>(at(rdev, pos_off[r]));
                 x.tile_base    = reinterpret_cast<unsigned*>(at(rdev, tbase_off[r]));
                 x.tile_cnt     = reinterpret_cast<unsigned short*>(at(rdev, tcnt_off[r]));
                 for (int q = 0; q < nown; ++q) {
                     x.queue[q] = reinterpret_cast<unsigned*>(at(std::get<0>(src_info[q]), queue_off[r][q]));
-                    x.cap[q]   = cap[r][q];
                     x.resp[q]  = reinterpret_cast<U*>(at(rdev, resp_off[r][q]));
                 }
             }
             std::vector<b200::gx_owner_t<U>> ow(nown);
             for (int q = 0; q < nown; ++q) {
-                auto& y     = ow[q];
-                y.src_local = src_base + size_t(q) * per;
-                y.nreq      = nreq;
+                auto& y        = ow[q];
+                y.src_local    = src_base + size_t(q) * per;
+                y.part_elems   = std::get<2>(src_info[q]) * src_lead;
+                y.nreq         = nreq;
+                y.regions      = regions;
+                y.region_shift = region_shift;
                 for (int r = 0; r < nreq; ++r) {
                     y.queue[r]   = rq[r].queue[q];
-                    y.counter[r] = rq[r].counters + q;
-                    y.cap[r]     = cap[r][q];
+                    y.counter[r] = rq[r].counters + size_t(q) * regions;
+                    y.cap[r]     = cap[r];
                     y.resp[r]    = rq[r].resp[q];
                 }
             }
+            static const int prefetch_mode = [] {
+                const char* e = std::getenv("SCLX_B200_GATHER_PREFETCH");
+                return e ? std::atoi(e) : 1;
+            }();
             // ---- three launch groups --------------------------------------------------------
             b200::for_each_partition(out, out_info, [&](const b200::partition_t& p) {
                 const auto& x = rq[p.ordinal];
                 if (x.n == 0) return;
                 cuda::cuda_exception::raise_if_not_success(
-                    cudaMemsetAsync(x.counters, 0, sizeof(unsigned) * b200::kGxMaxParts, p.stream),
+                    cudaMemsetAsync(x.counters, 0, sizeof(unsigned) * buckets, p.stream),
                     std::experimental::source_location::current(),
                     "sclx::algorithm::"
                 );
-                const unsigned grid
-                    = b200::persistent_grid(tiles_r[p.ordinal], 3, b200::sm_count_of(p.device));
+                // one tile per CTA (staggered CTA starts de-synchronise the load / bucket / store
+                // phases of the chip; a single resident wave runs them in lock step)
+                const unsigned grid = unsigned(std::min<size_t>(tiles_r[p.ordinal], size_t(1) << 20));
                 b200::gx_partition_kernel<U, index_t_>
                     <<<grid, b200::kGxThreads, 0, p.stream>>>(x, idx_ptr + p.offset);
             });
             b200::for_each_partition(src, src_info, [&](const b200::partition_t& p) {
                 unsigned max_cap = 0;
-                for (int r = 0; r < nreq; ++r) max_cap = std::max(max_cap, cap[r][p.ordinal]);
+                for (int r = 0; r < nreq; ++r) max_cap = std::max(max_cap, cap[r]);
                 if (max_cap == 0) return;
-                const dim3 grid((max_cap + b200::kGxServeChunk - 1) / b200::kGxServeChunk, unsigned(nreq));
-                b200::gx_serve_kernel<U><<<grid, b200::kGxServeThreads, 0, p.stream>>>(ow[p.ordinal]);
+                const dim3 grid(
+                    (max_cap + b200::kGxServeChunk - 1) / b200::kGxServeChunk, unsigned(nreq), regions
+                );
+                b200::gx_serve_kernel<U>
+                    <<<grid, b200::kGxServeThreads, 0, p.stream>>>(ow[p.ordinal], prefetch_mode);
             });
             b200::for_each_partition(out, out_info, [&](const b200::partition_t& p) {
                 const auto& x = rq[p.ordinal];
                 if (x.n == 0) return;
-                const unsigned grid
-                    = b200::persistent_grid(tiles_r[p.ordinal], 3, b200::sm_count_of(p.device));
+                const unsigned grid = unsigned(std::min<size_t>(tiles_r[p.ordinal], size_t(1) << 20));
                 b200::gx_place_kernel<U><<<grid, b200::kGxThreads, 0, p.stream>>>(x);
             });
         }
     }
     std::vector<int> devices = b200::devices_of(out_info);
-    for (int d : b200::devices_of(src_info)) devices.push_back(d);
+    for (int d : b200::devices_of(src_info))
+        if (std::find(devices.begin(), devices.end(), d) == devices.end()) devices.push_back(d);
     b200::sync_devices(devices);
     cuda::set_device(caller_device);
 }

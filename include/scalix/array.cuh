@@ -13,8 +13,12 @@
 //               all GPUs: local accesses hit HBM, cross-partition accesses are plain
 //               NVLink/NVSwitch peer loads, stores and atomics — nothing faults or migrates.
 //               Host code may still dereference elements (the reference's examples do):
-//               a software mirror at the same addresses is filled on first touch and
-//               written back before the next device access (runtime.cpp).
+//               a software mirror at the same addresses is filled on first touch (in spans
+//               that grow with sequential access) and written back before the next device
+//               access (runtime.cpp).  User-space loads and stores fault pages in; a SYSCALL
+//               (read(2), fread, recv ...) cannot, so bulk I/O into array memory goes after
+//               prefetch_async({cpu_device_id}), which makes the range host-resident,
+//               readable and writable, and pinned for PCIe-rate copies when it is large.
 //
 // The partition arithmetic is the reference's: the LAST dimension is split into contiguous
 // blocks of ceil(last/ndev) columns, surplus devices are dropped (ibid. :471-508).
@@ -505,8 +509,11 @@ class array {
     __host__ array& set_read_mostly() { return *this; }
     __host__ array& unset_read_mostly() { return *this; }
 
-    // "prefetch to the CPU" brings the host mirror up to date in one bulk copy; a prefetch to
-    // devices only makes pending host stores visible (pages never move on access).
+    // "prefetch to the CPU" makes the range HOST-RESIDENT in one bulk copy (per owner, in
+    // parallel): readable and writable without further faults — syscalls into it work, as on
+    // the reference's managed memory — and written back as a whole before the next device
+    // access.  A prefetch to devices only makes pending host stores visible (pages never move
+    // on access).
     __host__ std::future<void> prefetch_async(
         const std::vector<int>& device_ids,
         exec_topology topology = exec_topology::replicated
@@ -767,7 +774,12 @@ __host__ void serialize_array(Archive& archive, const sclx::array<T, Rank>& arra
 #ifndef __CUDA_ARCH__
     for (uint d = 0; d < Rank; ++d) archive(array.shape()[d]);
     if constexpr (std::is_same_v<Archive, cereal::BinaryInputArchive>) {
-        archive(cereal::binary_data(array.data().get(), array.elements() * sizeof(T)));
+        // loading into an existing array: staged, because a stream may hand the destination
+        // pointer straight to read(2), and a syscall cannot fault the host mirror in
+        using raw_t = std::remove_const_t<T>;
+        std::vector<raw_t> staged(array.elements());
+        archive(cereal::binary_data(staged.data(), staged.size() * sizeof(T)));
+        std::copy(staged.begin(), staged.end(), const_cast<raw_t*>(array.begin()));
     } else {
         std::for_each(array.begin(), array.end(), [&](auto& element) { archive(element); });
     }

@@ -1,29 +1,33 @@
-// scalix-b200: exchange form of the cross-partition gather  out[i] = src[index[i]].
+// scalix-b200: binned (exchange) form of the gather  out[i] = src[index[i]].
 //
-// Why it exists (experiments/p2p_probe.cu on 2 x B200, profiles/r01_p2p_probe.txt): NVLink 5
-// P2P serves about 6.5 G REQUESTS/s per GPU whatever the request carries — a random 4-byte
-// peer load, a 16-byte one, a posted 4-byte store and a fully coalesced 128-byte line all cost
-// one request.  A gather that issues one peer load per index (what a user lambda over the
-// range launcher does, and all an opaque lambda can do) is therefore capped at ~26 GB/s of
-// payload, 3 % of the link, while local HBM serves 40 G random 4-byte reads/s.  The exchange
-// form moves the same data in 128-byte requests only:
+// Two measured limits shape it (experiments/p2p_probe.cu, experiments/fetch_granularity.cu;
+// profiles/r01_p2p_probe.txt, r01_fetch_granularity.txt):
+//   * NVLink 5 P2P serves ~6.5 G REQUESTS/s per GPU whatever a request carries, so one peer load
+//     per index caps a cross-partition gather at ~26 GB/s of payload (3 % of the link);
+//   * local HBM serves ~40 G random 4-byte reads/s whatever the fetch granularity (a DRAM
+//     row-activation limit), although BASELINE config 4 wants one element per 16 source bytes,
+//     i.e. every 32-byte sector about twice.
+// Both go away when requests are BINNED by where their source element lives.  A bucket is one
+// L2-sized REGION of one owner's partition (regions x owners <= kGxMaxBuckets):
 //
-//   K1  partition (requester r, one CTA per 4096-index tile): classify every index by owning
-//       partition q, bucket the tile in shared memory, reserve a run in the (r -> q) request
-//       queue with ONE atomic per bucket and write the 32-bit in-partition offsets to the queue
-//       IN OWNER q's MEMORY with coalesced posted stores; keep the 16-bit in-tile positions
-//       locally, in the same order.
-//   K2  serve (owner q): stream its queues, gather from its LOCAL partition (HBM random reads)
-//       and write the values, in queue order, to the response buffer IN REQUESTER r's MEMORY
-//       (coalesced posted stores).
-//   K3  place (requester r): stream responses + positions, scatter inside the tile's 16 KiB
-//       window of `out`.
+//   K1  partition (requester r, one CTA per 4096-index tile): classify every index by bucket,
+//       bucket the tile in shared memory, reserve a run in the (r -> bucket) request queue with
+//       ONE atomic per bucket and write the 32-bit in-partition offsets to the queue IN THE
+//       OWNER'S MEMORY with coalesced posted stores; keep the 16-bit in-tile positions locally,
+//       in the same order, plus (first slot, length) of every run.
+//   K2  serve (owner q), region after region: while region s is served, its CTAs pull region
+//       s+1 into L2 with bulk prefetches (a sequential HBM stream); the gather loads of a region
+//       then HIT L2 instead of opening a DRAM row each.  Values go, in queue order, to the
+//       response buffer IN THE REQUESTER'S MEMORY (coalesced posted stores).
+//   K3  place (requester r): per tile, stream the responses of its runs + positions and scatter
+//       inside the tile's 16 KiB window of `out`.
 //
-// The three kernels are three launch groups (ordered across devices by stream events, no host
-// round trip).  Queues have bounded capacity (1.25 x the uniform share + one tile); an index
-// that finds its queue full is served by a direct peer load in K1, so skewed index sets stay
-// correct and merely lose the speed-up.  Pure data movement: results are bit-identical to the
-// direct gather whatever the order the queues were filled in.
+// On one GPU this is a three-pass streaming gather (48 algorithmic bytes per index instead of a
+// DRAM row activation); across GPUs only full-line NVLink writes cross the switch.  The three
+// kernels are three launch groups ordered by stream events, no host round trip.  Queues have
+// bounded capacity (1.25 x the uniform share + slack); an index that finds its queue full is
+// served by a direct (peer) load in K1, so skewed index sets stay correct and merely lose the
+// speed-up.  Pure data movement: results are bit-identical to the direct gather.
 #pragma once
 
 #include "primitives.cuh"
@@ -32,10 +36,12 @@
 
 namespace sclx::b200 {
 
-constexpr int kGxMaxParts  = 16;
-constexpr int kGxThreads   = 512;
-constexpr int kGxPerThread = 8;
-constexpr int kGxTile      = kGxThreads * kGxPerThread;  // 4096 indices per tile
+constexpr int kGxMaxParts     = 16;   // devices on either side
+constexpr int kGxMaxBuckets   = 512;  // owners x source regions
+constexpr int kGxThreads      = 512;
+constexpr int kGxPerThread    = 8;
+constexpr int kGxTile         = kGxThreads * kGxPerThread;  // 4096 indices per tile
+constexpr unsigned kGxRunAlign = 8;   // queue runs start on 32-byte sectors
 
 // e / per and e % per with one 64x64 high multiply (per is the same for every partition but
 // the last: ceil(last/ndev) * leading elements)
@@ -61,56 +67,92 @@ gx_owner(unsigned long long e, const gx_div_t& d, unsigned& q, unsigned& off) {
     off = unsigned(r);
 }
 
+// source element -> bucket: owner q (uniform blocks of `per` elements), region s inside the
+// owner's partition (2^region_shift elements each); bucket = q * regions + s
+struct gx_geometry_t {
+    gx_div_t div;
+    unsigned region_shift;
+    unsigned regions;  // per owner
+    unsigned buckets;  // nowners * regions
+};
+
 template<class U>  // U: unsigned carrier of the element width
 struct gx_requester_t {
     U* out;             // this partition of `out`
     const U* src_base;  // element 0 of the whole source (direct path when a queue is full)
     size_t n;           // indices in this partition
     int nowners;
-    gx_div_t div;
-    unsigned* queue[kGxMaxParts];  // (this requester -> q) offsets, in owner q's memory
-    unsigned cap[kGxMaxParts];     // capacity of that queue / response buffer (multiple of 32)
-    U* resp[kGxMaxParts];          // responses from owner q, local
-    unsigned* counters;            // [nowners] entries reserved so far, local
+    gx_geometry_t geo;
+    unsigned* queue[kGxMaxParts];  // (this requester -> owner q): [regions][cap] offsets, in q's memory
+    U* resp[kGxMaxParts];          // [regions][cap] responses from owner q, local
+    unsigned cap;                  // capacity of every bucket's queue (multiple of kGxRunAlign)
+    unsigned* counters;            // [buckets] entries reserved so far, local
     unsigned short* pos;           // [tiles * kGxTile] in-tile positions of queued entries
-    unsigned* tile_base;           // [tiles][nowners] first queue slot of the tile's run
-    unsigned short* tile_cnt;      // [tiles][nowners] length of that run
+    unsigned* tile_base;           // [tiles][buckets] first queue slot of the tile's run
+    unsigned short* tile_cnt;      // [tiles][buckets] length of that run
 };
 
 template<class U>
 struct gx_owner_t {
     const U* src_local;  // first element of this partition of the source
+    size_t part_elems;   // elements in it
     int nreq;
-    const unsigned* queue[kGxMaxParts];    // (r -> this owner) offsets, local
-    const unsigned* counter[kGxMaxParts];  // &counters_r[this owner], in requester r's memory
+    unsigned regions, region_shift;
+    const unsigned* queue[kGxMaxParts];    // (r -> this owner): [regions][cap[r]] offsets, local
+    const unsigned* counter[kGxMaxParts];  // &counters_r[this owner's first bucket], in r's memory
     unsigned cap[kGxMaxParts];
-    U* resp[kGxMaxParts];  // response buffer for this owner, in requester r's memory
+    U* resp[kGxMaxParts];  // [regions][cap[r]] response buffer, in requester r's memory
 };
 
+// exclusive prefix sum of cnt[0..n) into start[0..n], by warp 0 of the CTA (n <= kGxMaxBuckets)
+__device__ __forceinline__ void gx_scan_counts(const unsigned short* cnt, unsigned* start, int n) {
+    if (threadIdx.x >= 32) return;
+    const int lane = threadIdx.x;
+    const int per  = (n + 31) / 32;
+    const int lo = lane * per, hi = lo + per < n ? lo + per : n;
+    unsigned sum = 0;
+    for (int b = lo; b < hi; ++b) sum += cnt[b];
+    unsigned incl = sum;
+#pragma unroll
+    for (int d = 1; d < 32; d <<= 1) {
+        const unsigned up = __shfl_up_sync(0xffffffffu, incl, d);
+        if (lane >= d) incl += up;
+    }
+    unsigned run = incl - sum;
+    for (int b = lo; b < hi; ++b) {
+        start[b] = run;
+        run += cnt[b];
+    }
+    if (lane == 31) start[n] = incl;
+}
+
 // ---- K1 -----------------------------------------------------------------------------------
-// Per-thread state is packed (32-bit offset + owner<<16|rank) so three 512-thread CTAs fit an
-// SM; the first version kept the 64-bit indices live, needed 58 registers, ran two CTAs per SM
-// and was issue-bound at 1.0 ms for 2^27 indices (profiles/r01_ncu_gather_exchange_details.txt).
+// Per-thread state is packed (32-bit offset + bucket<<16|rank) so three 512-thread CTAs fit an
+// SM (profiles/r01_ncu_gather_exchange_details.txt: keeping the 64-bit indices live cost a CTA
+// per SM and made the kernel issue-bound).
 template<class U, class I>
 __global__ void __launch_bounds__(kGxThreads, 3)
     gx_partition_kernel(gx_requester_t<U> rq, const I* __restrict__ index) {
-    __shared__ unsigned s_off[kGxTile];
-    __shared__ unsigned short s_pos[kGxTile];
-    __shared__ unsigned s_cnt[kGxMaxParts], s_start[kGxMaxParts + 1], s_gbase[kGxMaxParts],
-        s_take[kGxMaxParts];
-    const unsigned tid   = threadIdx.x;
-    const unsigned lane  = tid & 31;
-    const unsigned below = (1u << lane) - 1u;
-    const int nown       = rq.nowners;
-    const size_t tiles   = (rq.n + kGxTile - 1) / kGxTile;
+    // one 64-bit record per queued index, in slot order: offset | bucket << 32 | position << 48
+    // (one shared-memory store when the tile is bucketed, one load when it is written out)
+    __shared__ unsigned long long s_rec[kGxTile];
+    __shared__ unsigned s_cnt[kGxMaxBuckets];
+    __shared__ unsigned s_span[kGxMaxBuckets + 1];  // first slot | entries taken << 16, per bucket
+    __shared__ unsigned s_start[kGxMaxBuckets + 1];
+    __shared__ unsigned* s_run[kGxMaxBuckets];  // where the tile's run of each bucket starts in its queue
+    __shared__ unsigned short s_take[kGxMaxBuckets];
+    const unsigned tid     = threadIdx.x;
+    const unsigned nb      = rq.geo.buckets;
+    const unsigned regions = rq.geo.regions;
+    const size_t tiles     = (rq.n + kGxTile - 1) / kGxTile;
 
     for (size_t t = blockIdx.x; t < tiles; t += gridDim.x) {
-        if (tid < unsigned(nown)) s_cnt[tid] = 0;
+        for (unsigned b = tid; b < nb; b += kGxThreads) s_cnt[b] = 0;
         __syncthreads();
         const size_t tbase   = t * kGxTile;
         const unsigned avail = unsigned(rq.n - tbase < size_t(kGxTile) ? rq.n - tbase : size_t(kGxTile));
         const I* __restrict__ tile_index = index + tbase;
-        unsigned off[kGxPerThread], qr[kGxPerThread];  // qr = owner << 16 | rank in (tile, owner)
+        unsigned off[kGxPerThread], br[kGxPerThread];  // br = bucket << 16 | rank in (tile, bucket)
         {
             unsigned long long e[kGxPerThread];
 #pragma unroll
@@ -121,53 +163,51 @@ __global__ void __launch_bounds__(kGxThreads, 3)
 #pragma unroll
             for (int k = 0; k < kGxPerThread; ++k) {
                 const bool valid = unsigned(k) * kGxThreads + tid < avail;
-                unsigned q       = 0xffu;
+                unsigned b       = 0xffffu;
                 off[k]           = 0;
                 if (valid) {
-                    gx_owner(e[k], rq.div, q, off[k]);
-                    if (q >= unsigned(nown)) q = unsigned(nown) - 1;  // out of range: UB upstream too
+                    unsigned q = 0;
+                    if (rq.nowners == 1) off[k] = unsigned(e[k]);  // one owner: no division
+                    else gx_owner(e[k], rq.geo.div, q, off[k]);
+                    if (q >= unsigned(rq.nowners)) q = unsigned(rq.nowners) - 1;  // out of range: UB upstream too
+                    unsigned s = off[k] >> rq.geo.region_shift;
+                    if (s >= regions) s = regions - 1;
+                    b = q * regions + s;
                 }
-                // one shared-memory atomic per (warp, owner)
-                const unsigned peers = __match_any_sync(0xffffffffu, q);
-                const int leader     = __ffs(peers) - 1;
-                unsigned first       = 0;
-                if (int(lane) == leader && valid) first = atomicAdd(&s_cnt[q], unsigned(__popc(peers)));
-                first = __shfl_sync(0xffffffffu, first, leader);
-                qr[k] = (q << 16) | (first + unsigned(__popc(peers & below)));
+                // rank inside (tile, bucket): one shared-memory atomic per index.  With hundreds
+                // of buckets the lanes of a warp rarely collide; aggregating equal buckets with
+                // __match_any_sync first cost 3x the whole kernel (profiles/r02_ncu_gather_binned_v1.txt)
+                br[k] = valid ? ((b << 16) | atomicAdd(&s_cnt[b], 1u)) : 0xffffffffu;
             }
         }
         __syncthreads();
-        if (tid < unsigned(nown)) {
-            // runs are reserved in multiples of 32 entries, so every run starts on a 128-byte
-            // line of the queue and a warp's store of 32 offsets is one full-line NVLink write
-            const unsigned c    = s_cnt[tid];
-            const unsigned g    = c ? atomicAdd(&rq.counters[tid], (c + 31u) & ~31u) : 0u;
-            const unsigned room = g < rq.cap[tid] ? rq.cap[tid] - g : 0u;
+        for (unsigned b = tid; b < nb; b += kGxThreads) {
+            // runs are reserved in multiples of kGxRunAlign entries: every run starts on a
+            // 32-byte sector of the queue and of the response buffer
+            const unsigned c    = s_cnt[b];
+            const unsigned g    = c ? atomicAdd(&rq.counters[b], (c + kGxRunAlign - 1u) & ~(kGxRunAlign - 1u)) : 0u;
+            const unsigned room = g < rq.cap ? rq.cap - g : 0u;
             const unsigned take = c < room ? c : room;
-            s_gbase[tid]        = g;
-            s_take[tid]         = take;
-            rq.tile_base[t * nown + tid] = g;
-            rq.tile_cnt[t * nown + tid]  = (unsigned short)take;
+            const unsigned q    = b / regions, sub = b - q * regions;
+            s_run[b]            = rq.queue[q] + size_t(sub) * rq.cap + g;
+            s_take[b]           = (unsigned short)take;
+            rq.tile_base[t * nb + b] = g;
+            rq.tile_cnt[t * nb + b]  = (unsigned short)take;
         }
         __syncthreads();
-        if (tid == 0) {
-            unsigned acc = 0;
-            for (int o = 0; o < nown; ++o) {
-                s_start[o] = acc;
-                acc += s_take[o];
-            }
-            s_start[nown] = acc;
-        }
+        gx_scan_counts(s_take, s_start, int(nb));
+        __syncthreads();
+        for (unsigned b = tid; b < nb; b += kGxThreads) s_span[b] = s_start[b] | (unsigned(s_take[b]) << 16);
         __syncthreads();
 #pragma unroll
         for (int k = 0; k < kGxPerThread; ++k) {
             const unsigned j = unsigned(k) * kGxThreads + tid;
             if (j < avail) {
-                const unsigned q = qr[k] >> 16, rank = qr[k] & 0xffffu;
-                if (rank < s_take[q]) {
-                    const unsigned slot = s_start[q] + rank;
-                    s_off[slot]         = off[k];
-                    s_pos[slot]         = (unsigned short)j;
+                const unsigned b = br[k] >> 16, rank = br[k] & 0xffffu;
+                const unsigned span = s_span[b];
+                if (rank < (span >> 16)) {
+                    s_rec[(span & 0xffffu) + rank]
+                        = (unsigned long long)off[k] | ((unsigned long long)b << 32) | ((unsigned long long)j << 48);
                 } else {
                     // queue full: direct (peer) load
                     rq.out[tbase + j] = rq.src_base[(unsigned long long)__ldg(tile_index + j)];
@@ -175,24 +215,24 @@ __global__ void __launch_bounds__(kGxThreads, 3)
             }
         }
         __syncthreads();
-        const unsigned total = s_start[nown];
-        for (int o = 0; o < nown; ++o) {
-            const unsigned take = s_take[o], padded = (take + 31u) & ~31u;  // padding reads offset 0
-            unsigned* __restrict__ queue = rq.queue[o] + s_gbase[o];
-            const unsigned first         = s_start[o];
-            for (unsigned j = tid; j < padded; j += kGxThreads) queue[j] = j < take ? s_off[first + j] : 0u;
+        const unsigned total = s_start[nb];
+        for (unsigned i = tid; i < total; i += kGxThreads) {
+            // slots of one bucket are consecutive: a warp writes whole runs, coalesced
+            const unsigned long long rec = s_rec[i];
+            const unsigned b    = unsigned(rec >> 32) & 0xffffu;
+            const unsigned span = s_span[b];
+            const unsigned r = i - (span & 0xffffu), take = span >> 16;
+            unsigned* __restrict__ run = s_run[b];
+            run[r]                     = unsigned(rec);
+            if (r + 1 == take)  // the run's padding slots are served too: make them harmless
+                for (unsigned p = take; p < ((take + kGxRunAlign - 1u) & ~(kGxRunAlign - 1u)); ++p) run[p] = 0u;
+            rq.pos[tbase + i] = (unsigned short)(rec >> 48);
         }
-        for (unsigned i = tid; i < total; i += kGxThreads) rq.pos[tbase + i] = s_pos[i];
         __syncthreads();
     }
 }
 
 // ---- K2 -----------------------------------------------------------------------------------
-// One random 4/8-byte load per entry: bound by the HBM's random-access rate, not by bytes.
-// experiments/serve_tune.cu (profiles/r01_serve_tune.txt): a persistent grid in lock step
-// serves 36-37 G loads/s, many small CTAs (one 1024-entry chunk each, no loop) 47-48 G/s —
-// the staggered CTA starts de-synchronise the queue-read / random-read / store phases.  The
-// L2::64B hint halves the DRAM bytes fetched per load (126 -> 63).
 template<class U>
 __device__ __forceinline__ U gx_load_random(const U* p) {
     if constexpr (sizeof(U) == 4) {
@@ -208,20 +248,49 @@ __device__ __forceinline__ U gx_load_random(const U* p) {
     }
 }
 
+// sequential pull of [begin, end) into L2 (one instruction for the whole range)
+__device__ __forceinline__ void gx_prefetch_l2(const void* begin, const void* end) {
+    unsigned long long a0 = reinterpret_cast<unsigned long long>(begin) & ~15ull;
+    unsigned long long a1 = (reinterpret_cast<unsigned long long>(end) + 15ull) & ~15ull;
+    if (a1 <= a0) return;
+    asm volatile("cp.async.bulk.prefetch.L2.global [%0], %1;" ::"l"(a0), "r"(unsigned(a1 - a0)) : "memory");
+}
+
 constexpr int kGxServeThreads = 256, kGxServeUnroll = 4;
 constexpr int kGxServeChunk   = kGxServeThreads * kGxServeUnroll;
 
-// grid = (ceil(max cap / chunk), nreq): CTA (x, r) serves entries [x*chunk, (x+1)*chunk) of
-// requester r's queue; CTAs beyond the queue's fill level exit at once
+// grid = (ceil(max cap / chunk), nreq, regions): CTA (x, r, s) serves entries
+// [x*chunk, (x+1)*chunk) of requester r's queue for region s of this owner.  CTAs are
+// dispatched x-fastest, region-slowest, so the chip works on one region (plus the tail of the
+// previous one) at a time; every CTA first pulls its slice of region s+1 into L2.  CTAs beyond
+// a queue's fill level exit once their prefetch is issued.  One chunk per CTA and no loop:
+// staggered CTA starts de-synchronise the queue-read / gather / store phases
+// (experiments/serve_tune.cu, profiles/r01_serve_tune.txt).
 template<class U>
-__global__ void __launch_bounds__(kGxServeThreads) gx_serve_kernel(gx_owner_t<U> ow) {
-    const int r  = blockIdx.y;
-    unsigned cnt = __ldcg(ow.counter[r]);
+__global__ void __launch_bounds__(kGxServeThreads) gx_serve_kernel(gx_owner_t<U> ow, int prefetch) {
+    const unsigned s = blockIdx.z;
+    const int r      = blockIdx.y;
+    if (prefetch && threadIdx.x == 0) {
+        // region 0 has no predecessor: its own CTAs pull it (late for some, still a stream)
+        const unsigned target     = (s + 1 < ow.regions && prefetch == 1) ? s + 1 : s;
+        const bool wanted         = target != s || s == 0;
+        const size_t region_elems = size_t(1) << ow.region_shift;
+        const size_t first        = size_t(target) * region_elems;
+        if (wanted && first < ow.part_elems) {
+            const size_t last   = first + region_elems < ow.part_elems ? first + region_elems : ow.part_elems;
+            const size_t slices = size_t(gridDim.x) * gridDim.y;
+            const size_t slice  = size_t(blockIdx.y) * gridDim.x + blockIdx.x;
+            size_t step         = ((last - first + slices - 1) / slices + 31) & ~size_t(31);
+            const size_t lo     = first + slice * step;
+            if (lo < last) gx_prefetch_l2(ow.src_local + lo, ow.src_local + (lo + step < last ? lo + step : last));
+        }
+    }
+    unsigned cnt = __ldcg(ow.counter[r] + s);
     if (cnt > ow.cap[r]) cnt = ow.cap[r];
     const unsigned base = blockIdx.x * unsigned(kGxServeChunk);
     if (base >= cnt) return;
-    const unsigned* __restrict__ queue = ow.queue[r] + base;
-    U* __restrict__ resp               = ow.resp[r] + base;
+    const unsigned* __restrict__ queue = ow.queue[r] + size_t(s) * ow.cap[r] + base;
+    U* __restrict__ resp               = ow.resp[r] + size_t(s) * ow.cap[r] + base;
     const unsigned left                = cnt - base;
     unsigned o[kGxServeUnroll];
     U v[kGxServeUnroll];
@@ -235,46 +304,75 @@ __global__ void __launch_bounds__(kGxServeThreads) gx_serve_kernel(gx_owner_t<U>
 #pragma unroll
     for (int u = 0; u < kGxServeUnroll; ++u) {
         const unsigned i = unsigned(u) * kGxServeThreads + threadIdx.x;
-        if (i < left) resp[i] = v[u];
+        if (i < left) __stcs(resp + i, v[u]);
     }
 }
 
 // ---- K3 -----------------------------------------------------------------------------------
+// One tile per CTA trip.  The tile's runs are laid out back to back in slot order (the order K1
+// wrote `pos` in); the warps first expand the run table into a slot -> bucket map in shared
+// memory, then every thread moves 8 slots with 8 independent loads in flight: response value
+// (coalesced inside a run) + position.  The values are un-permuted in SHARED memory and the
+// tile's window of `out` is written with full-width coalesced stores (one scattered 4-byte
+// store per index is one L2 request per index: profiles/r02_gather_v2_launches.csv).  Indices
+// K1 served directly (queue overflow) are already in `out` and are left alone.
 template<class U>
-__global__ void __launch_bounds__(kGxThreads) gx_place_kernel(gx_requester_t<U> rq) {
-    __shared__ unsigned s_start[kGxMaxParts + 1], s_gbase[kGxMaxParts];
-    const int tid      = threadIdx.x;
-    const int nown     = rq.nowners;
-    const size_t tiles = (rq.n + kGxTile - 1) / kGxTile;
+__global__ void __launch_bounds__(kGxThreads, 3) gx_place_kernel(gx_requester_t<U> rq) {
+    __shared__ U s_val[kGxTile];
+    __shared__ unsigned s_start[kGxMaxBuckets + 1];
+    __shared__ const U* s_run[kGxMaxBuckets];
+    __shared__ unsigned short s_take[kGxMaxBuckets], s_bkt[kGxTile];
+    __shared__ unsigned s_written[kGxTile / 32];  // bit per window slot: value came through a queue
+    const unsigned tid     = threadIdx.x;
+    const unsigned lane    = tid & 31, warp = tid >> 5;
+    const unsigned nb      = rq.geo.buckets;
+    const unsigned regions = rq.geo.regions;
+    const size_t tiles     = (rq.n + kGxTile - 1) / kGxTile;
     for (size_t t = blockIdx.x; t < tiles; t += gridDim.x) {
-        if (tid == 0) {
-            unsigned acc = 0;
-            for (int o = 0; o < nown; ++o) {
-                s_start[o] = acc;
-                s_gbase[o] = rq.tile_base[t * nown + o];
-                acc += rq.tile_cnt[t * nown + o];
-            }
-            s_start[nown] = acc;
+        for (unsigned b = tid; b < nb; b += kGxThreads) {
+            const unsigned q = b / regions, sub = b - q * regions;
+            s_run[b]  = rq.resp[q] + size_t(sub) * rq.cap + __ldcs(rq.tile_base + t * nb + b);
+            s_take[b] = __ldcs(rq.tile_cnt + t * nb + b);
+        }
+        if (tid < kGxTile / 32) s_written[tid] = 0;
+        __syncthreads();
+        gx_scan_counts(s_take, s_start, int(nb));
+        __syncthreads();
+        for (unsigned b = warp; b < nb; b += kGxThreads / 32) {
+            const unsigned first = s_start[b], take = s_take[b];
+            for (unsigned j = lane; j < take; j += 32) s_bkt[first + j] = (unsigned short)b;
         }
         __syncthreads();
         const size_t tbase   = t * kGxTile;
-        const unsigned total = s_start[nown];
+        const unsigned avail = unsigned(rq.n - tbase < size_t(kGxTile) ? rq.n - tbase : size_t(kGxTile));
+        const unsigned total = s_start[nb];
         U v[kGxPerThread];
         unsigned short p[kGxPerThread];
 #pragma unroll
         for (int k = 0; k < kGxPerThread; ++k) {
             const unsigned i = unsigned(k) * kGxThreads + tid;
             if (i < total) {
-                int o = 0;
-                while (i >= s_start[o + 1]) ++o;
-                v[k] = __ldcs(rq.resp[o] + s_gbase[o] + (i - s_start[o]));
-                p[k] = __ldcs(rq.pos + tbase + i);
+                const unsigned b = s_bkt[i];
+                v[k]             = __ldcs(s_run[b] + (i - s_start[b]));
+                p[k]             = __ldcs(rq.pos + tbase + i);
             }
         }
 #pragma unroll
         for (int k = 0; k < kGxPerThread; ++k) {
             const unsigned i = unsigned(k) * kGxThreads + tid;
-            if (i < total) rq.out[tbase + p[k]] = v[k];
+            if (i < total) {
+                s_val[p[k]] = v[k];
+                if (total != avail) atomicOr(&s_written[p[k] >> 5], 1u << (p[k] & 31));
+            }
+        }
+        __syncthreads();
+        U* __restrict__ window = rq.out + tbase;
+        if (total == avail) {
+            // the common case: every index of the tile went through a queue
+            for (unsigned j = tid; j < avail; j += kGxThreads) window[j] = s_val[j];
+        } else {
+            for (unsigned j = tid; j < avail; j += kGxThreads)
+                if (s_written[j >> 5] >> (j & 31) & 1u) window[j] = s_val[j];
         }
         __syncthreads();
     }

@@ -36,7 +36,8 @@ inline cudaError_t range_launch_grid(
     size_t dynamic_smem,
     size_t user_grid_size,  // SIZE_MAX = default
     unsigned* grid_out,
-    size_t max_thread_count = std::numeric_limits<size_t>::max()
+    size_t max_thread_count = std::numeric_limits<size_t>::max(),
+    size_t leading_elements = 1  // product of the range's leading extents (1 for rank 1)
 ) {
     size_t blocks = (elements + block_threads - 1) / block_threads;
     if (blocks == 0) blocks = 1;
@@ -64,6 +65,20 @@ inline cudaError_t range_launch_grid(
     }
     if (blocks > 0x7fffffffull) blocks = 0x7fffffffull;
     if (blocks == 0) blocks = 1;
+    // Rank > 1: make the grid stride a whole number of "columns" (multiple of the leading
+    // extents' product) when that costs at most a few percent of the grid: a thread's
+    // successive elements then differ in the LAST coordinate only and the kernel advances its
+    // md-index with one add instead of a carry chain (dispatch.cuh)
+    if (leading_elements > 1 && user_grid_size == std::numeric_limits<size_t>::max()) {
+        size_t a = leading_elements, b = block_threads;
+        while (b) {
+            const size_t r = a % b;
+            a = b;
+            b = r;
+        }
+        const size_t unit = leading_elements / a;  // grid must be a multiple of this
+        if (unit > 1 && blocks >= 32 * unit) blocks -= blocks % unit;
+    }
     *grid_out = unsigned(blocks);
     return cudaSuccess;
 }

@@ -21,6 +21,7 @@
 #include "b200/dispatch.cuh"
 #include "b200/launch_config.cuh"
 
+#include <cstdlib>
 #include <iostream>
 #include <mutex>
 #include <string>
@@ -112,7 +113,35 @@ void run_launch_group(const device_info_t& device_info, Issue&& issue) {
     }
     cuda::set_device(caller_device);
     cuda::detail::check_rt(sclx_b200_rt_end_launch(n, devices.data()));
+    sclx_b200_note_launches(static_cast<unsigned long long>(n));
     for (int d : devices) launch_record::note(d);
+}
+
+// which captured arrays the range kernel prefetches one trip ahead (prefetch_plan_t,
+// b200/dispatch.cuh).  SCLX_B200_DISPATCH_PREFETCH=0 switches it off.
+template<class Functor>
+prefetch_plan_t make_prefetch_plan(const Functor& f, size_t range_elements) {
+    prefetch_plan_t plan;
+    static const bool enabled = [] {
+        const char* e = std::getenv("SCLX_B200_DISPATCH_PREFETCH");
+        return !(e && e[0] == '0');
+    }();
+    // small launches are latency-bound: not worth the scan
+    if (!enabled || range_elements < (size_t(1) << 16)) return plan;
+    void* bases[prefetch_plan_t::max_arrays];
+    size_t bytes[prefetch_plan_t::max_arrays];
+    const int found = sclx_b200_rt_find_captured_arrays(
+        &f, sizeof(Functor) <= 1024 ? sizeof(Functor) : 1024, prefetch_plan_t::max_arrays, bases, bytes
+    );
+    for (int k = 0; k < found; ++k) {
+        if (bytes[k] % range_elements != 0) continue;
+        const size_t per = bytes[k] / range_elements;
+        // 16 bytes per range element is far more often a LARGER array indexed indirectly (a
+        // gather source) than an array of 16-byte elements: leave those alone
+        if (per != 1 && per != 2 && per != 4 && per != 8) continue;
+        plan.add(bases[k], unsigned(per));
+    }
+    return plan;
 }
 
 template<class Kernel>
@@ -145,6 +174,7 @@ struct tag_executor {
         using functor_t = std::decay_t<F>;
         auto kernel     = Kernels::template range<functor_t, RangeRank, ThreadBlockRank>();
         const unsigned block_threads = unsigned(block_shape.elements());
+        const prefetch_plan_t plan = make_prefetch_plan<functor_t>(f, global_range.elements());
         nvtx_range trace("sclx range launch", typeid(Kernels).name());
         std::unique_lock<std::mutex> debug_lock(_debug_kernel_mutex::get(), std::defer_lock);
         if constexpr (_debug_kernel_launch) {
@@ -174,13 +204,14 @@ struct tag_executor {
                 cuda::cuda_exception::raise_if_not_success(
                     sclx::b200::range_launch_grid(
                         kernel, elements, block_threads, local_mem_size, grid_size, &grid,
-                        sclx::cuda::traits::kernel::max_thread_count()
+                        sclx::cuda::traits::kernel::max_thread_count(),
+                        global_range[RangeRank - 1] ? global_range.elements() / global_range[RangeRank - 1] : 1
                     ),
                     std::experimental::source_location::current(),
                     "sclx::detail::"
                 );
                 allow_dynamic_shared_memory(kernel, local_mem_size);
-                kernel<<<grid, block_threads, local_mem_size, stream>>>(f, metadata);
+                kernel<<<grid, block_threads, local_mem_size, stream>>>(f, metadata, plan);
             }
         );
         if constexpr (_debug_kernel_launch)
@@ -263,8 +294,12 @@ struct default_kernel_tag : tag_executor<default_kernels> {};
 // with the default_kernel_tag interface; use as `handler.launch<Tag>(...)`.
 #define REGISTER_SCALIX_KERNEL_TAG(Tag)                                                          \
     template<class F, uint RangeRank, uint ThreadBlockRank>                                      \
-    __global__ void sclx_##Tag(F f, sclx::kernel_info<RangeRank, ThreadBlockRank> metadata) {    \
-        sclx::detail::range_kernel_body(f, metadata);                                            \
+    __global__ void sclx_##Tag(                                                                  \
+        F f,                                                                                     \
+        sclx::kernel_info<RangeRank, ThreadBlockRank> metadata,                                  \
+        sclx::detail::prefetch_plan_t plan                                                       \
+    ) {                                                                                          \
+        sclx::detail::range_kernel_body(f, metadata, plan);                                      \
     }                                                                                            \
     template<class F, class IndexGenerator, uint ThreadBlockRank>                                \
     __global__ void sclx_##Tag(                                                                  \

@@ -191,6 +191,10 @@ int sclx_b200_array_free(void* base);
 int sclx_b200_array_repartition(void* base, int nparts, const int* devices,
                                 const size_t* byte_starts);
 int sclx_b200_array_owner(const void* ptr);       /* logical device holding the page, or -1 */
+/* runtime arrays whose base address appears as an 8-byte word inside `closure` (a device lambda's
+ * by-value captures): up to max_out (base, bytes) pairs; returns how many were found */
+int sclx_b200_rt_find_captured_arrays(const void* closure, size_t closure_bytes, int max_out,
+                                      void** bases, size_t* bytes);
 
 /* host/device coherence of the mirror */
 int sclx_b200_rt_before_device_access(void);      /* write back host stores, drop host copies */
@@ -238,8 +242,10 @@ int sclx_b200_rt_pool_release(void);
 /* per-device peer-visible grow-only workspace of sclx::algorithm::gather (exchange form) */
 int sclx_b200_rt_exchange_workspace(int logical, size_t bytes, void** ptr);
 
-/* number of kernels this library has launched in this process (monotonic) */
+/* number of kernels launched in this process by this library and by the header API's launch
+ * groups, which report theirs through note_launches (monotonic) */
 unsigned long long sclx_b200_launch_count(void);
+unsigned long long sclx_b200_note_launches(unsigned long long n);
 
 #ifdef __cplusplus
 }

@@ -62,6 +62,7 @@ ABI = {
     "sclx_b200_reduce_last_dim_host": (_i, [_vp, _sz, _sz, _i, _i, _vp, _vp]),
     "sclx_b200_inclusive_scan_host": (_i, [_vp, _vp, _sz, _i, _i]),
     "sclx_b200_launch_count": (C.c_ulonglong, []),
+    "sclx_b200_note_launches": (C.c_ulonglong, [C.c_ulonglong]),
     # runtime under the sclx:: header API
     "sclx_b200_rt_init": (_i, []),
     "sclx_b200_rt_set_emulated_devices": (_i, [_i]),
@@ -73,6 +74,7 @@ ABI = {
     "sclx_b200_array_free": (_i, [_vp]),
     "sclx_b200_array_repartition": (_i, [_vp, _i, _vp, _vp]),
     "sclx_b200_array_owner": (_i, [_vp]),
+    "sclx_b200_rt_find_captured_arrays": (_i, [_vp, _sz, _i, _pp, _vp]),
     "sclx_b200_rt_before_device_access": (_i, []),
     "sclx_b200_rt_prefetch_to_host": (_i, [_vp, _sz]),
     "sclx_b200_rt_quiesce": (_i, []),

@@ -6,6 +6,7 @@
 #include "scalix/detail/b200/dispatch.cuh"
 #include "scalix/detail/b200/launch_config.cuh"
 
+#include <initializer_list>
 #include <string>
 
 extern "C" unsigned long long sclx_b200_note_launches(unsigned long long n);
@@ -13,8 +14,20 @@ extern "C" int sclx_b200_set_error(int code, const char* msg);
 
 namespace {
 
+// `streamed`: the arrays the lambda walks element by element, {pointer, bytes per element} —
+// what sclx_b200_rt_find_captured_arrays finds by itself when the lambda captured sclx::arrays
+// (these entry points take raw device pointers, so the caller of launch_partitions names them)
+struct streamed_array {
+    const void* base;
+    unsigned elem_bytes;
+};
+
 template<uint Rank, class F>
-int launch_partitions(const sclx::md_range_t<Rank>& range, int nparts, cudaStream_t stream, F f) {
+int launch_partitions(const sclx::md_range_t<Rank>& range, int nparts, cudaStream_t stream, F f,
+                      std::initializer_list<streamed_array> streamed) {
+    sclx::detail::prefetch_plan_t plan;
+    if (range.elements() >= (size_t(1) << 16))
+        for (const auto& a : streamed) plan.add(a.base, a.elem_bytes);
     if (nparts < 1) return sclx_b200_set_error(SCLX_E_INVALID_ARGUMENT, "nparts must be >= 1");
     size_t start[64], len[64];
     if (nparts > 64) nparts = 64;
@@ -33,7 +46,7 @@ int launch_partitions(const sclx::md_range_t<Rank>& range, int nparts, cudaStrea
         unsigned grid = 0;
         cudaError_t e = sclx::b200::range_launch_grid(kernel, elems, 256, 0, ~size_t(0), &grid);
         if (e != cudaSuccess) return sclx_b200_set_error(int(e), cudaGetErrorString(e));
-        kernel<<<grid, 256, 0, stream>>>(f, info);
+        kernel<<<grid, 256, 0, stream>>>(f, info, plan);
         sclx_b200_note_launches(1);
         e = cudaGetLastError();
         if (e != cudaSuccess) return sclx_b200_set_error(int(e), cudaGetErrorString(e));
@@ -52,7 +65,8 @@ int sclx_b200_axpy_f32(float a, const void* x_, void* y_, size_t n, int nparts, 
         sclx::md_range_t<1>{n}, nparts, (cudaStream_t)stream,
         [=] __device__(const sclx::md_index_t<1>& idx, const sclx::kernel_info<1, 1>&) {
             y[idx[0]] = a * x[idx[0]] + y[idx[0]];
-        });
+        },
+        {{x, 4}, {y, 4}});
 }
 
 int sclx_b200_axpy_f32_rank3(float a, const void* x_, void* y_, size_t d0, size_t d1, size_t last,
@@ -65,7 +79,8 @@ int sclx_b200_axpy_f32_rank3(float a, const void* x_, void* y_, size_t d0, size_
         [=] __device__(const sclx::md_index_t<3>& idx, const sclx::kernel_info<3, 1>&) {
             const size_t i = idx.as_linear(shape);
             y[i]           = a * x[i] + y[i];
-        });
+        },
+        {{x, 4}, {y, 4}});
 }
 
 int sclx_b200_gather_launch_f32(const void* index_, size_t n, const void* src_, void* out_,
@@ -77,7 +92,8 @@ int sclx_b200_gather_launch_f32(const void* index_, size_t n, const void* src_, 
         sclx::md_range_t<1>{n}, nparts, (cudaStream_t)stream,
         [=] __device__(const sclx::md_index_t<1>& idx, const sclx::kernel_info<1, 1>&) {
             out[idx[0]] = src[index[idx[0]]];
-        });
+        },
+        {{index, 8}, {out, 4}});
 }
 
 }  // extern "C"

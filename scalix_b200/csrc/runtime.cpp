@@ -27,6 +27,7 @@
 #include <atomic>
 #include <cerrno>
 #include <csignal>
+#include <cstdint>
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
@@ -306,7 +307,22 @@ int for_each_piece(const allocation& al, size_t off, size_t len, F&& f) {
 // physical-run boundaries.  A pinned mirror moves each piece asynchronously on its owner's
 // stream (several GPUs = several PCIe links at once) and waits for all of them at the end; a
 // pageable one uses blocking copies.
-int copy_pieces(allocation& al, size_t off, size_t len, bool to_host) {
+int wait_for_copies(std::vector<int>& used) {
+    int cur = 0, rc = 0;
+    cudaGetDevice(&cur);
+    for (int d : used) {
+        cudaSetDevice(g_rt.dev[d].physical);
+        cudaError_t e = cudaStreamSynchronize(g_rt.dev[d].stream);
+        if (e != cudaSuccess && rc == 0) rc = rt_fail(e, "cudaStreamSynchronize");
+    }
+    cudaSetDevice(cur);
+    used.clear();
+    return rc;
+}
+
+// `pending`: when given, the copies of a pinned mirror are only QUEUED and their devices added
+// to it; the caller overlaps host work with the DMA and calls wait_for_copies() afterwards
+int copy_pieces(allocation& al, size_t off, size_t len, bool to_host, std::vector<int>* pending = nullptr) {
     if (len == 0) return 0;
     if (!al.pinned)
         return for_each_piece(al, off, len, [&](size_t o, size_t piece) -> int {
@@ -326,13 +342,14 @@ int copy_pieces(allocation& al, size_t off, size_t len, bool to_host) {
         if (std::find(used.begin(), used.end(), owner) == used.end()) used.push_back(owner);
         return 0;
     });
-    for (int d : used) {
-        cudaSetDevice(g_rt.dev[d].physical);
-        cudaError_t e = cudaStreamSynchronize(g_rt.dev[d].stream);
-        if (e != cudaSuccess && rc == 0) rc = rt_fail(e, "cudaStreamSynchronize");
-    }
     cudaSetDevice(cur);
-    return rc;
+    if (pending) {
+        for (int d : used)
+            if (std::find(pending->begin(), pending->end(), d) == pending->end()) pending->push_back(d);
+        return rc;
+    }
+    const int wrc = wait_for_copies(used);
+    return rc ? rc : wrc;
 }
 
 // bring chunks [c0, c1) of the host mirror up to date (device -> host); `for_write` leaves them
@@ -376,6 +393,9 @@ int fetch_chunks(allocation& al, size_t c0, size_t c1, bool for_write) {
 int flush_and_invalidate(allocation& al) {
     if (al.n_valid == 0) return 0;
     const size_t nchunks = al.state.size();
+    // pinned mirror: the write-back DMA reads physical pages, so the page-table work of the
+    // invalidation below (mprotect over gigabytes is tens of milliseconds) runs under it
+    std::vector<int> pending;
     size_t c = 0;
     while (c < nchunks) {
         if (al.state[c] == kInvalid) { ++c; continue; }
@@ -389,7 +409,7 @@ int flush_and_invalidate(allocation& al) {
             while (f < e && al.state[f] == kDirty) ++f;
             size_t off = d * kMirrorChunk, len = (f - d) * kMirrorChunk;
             if (off + len > al.va_bytes) len = al.va_bytes - off;
-            if (int rc = copy_pieces(al, off, len, /*to_host=*/false)) return rc;
+            if (int rc = copy_pieces(al, off, len, /*to_host=*/false, &pending)) return rc;
             g_rt.flushed_chunks += f - d;
             d = f;
         }
@@ -404,7 +424,7 @@ int flush_and_invalidate(allocation& al) {
     al.n_valid    = 0;
     al.fault_next = ~size_t(0);
     al.fault_span = 1;
-    return 0;
+    return wait_for_copies(pending);
 }
 
 constexpr size_t kMaxFaultSpan = 256;  // chunks: 16 MiB
@@ -822,6 +842,33 @@ int sclx_b200_array_repartition(void* base, int nparts, const int* devices, cons
     }
     CU(g_drv.MemSetAccess((CUdeviceptr)al->base, al->va_bytes, acc.data(), acc.size()));
     return sclx_b200_array_free(tmp);
+}
+
+// Arrays captured BY VALUE in a device lambda: scan the closure's object representation for
+// 8-byte words that are the base address of a live runtime array.  The range dispatcher pulls
+// the next grid-stride trip of such arrays into L2 while the current trip's loads are in
+// flight (detail/b200/dispatch.cuh); a wrong guess costs a useless prefetch, never a fault.
+int sclx_b200_rt_find_captured_arrays(const void* closure, size_t closure_bytes, int max_out, void** bases,
+                                      size_t* bytes) {
+    if (!closure || !bases || !bytes || max_out <= 0 || !g_rt.initialised) return 0;
+    const char* p   = static_cast<const char*>(closure);
+    const size_t lo = (8 - (reinterpret_cast<uintptr_t>(p) & 7)) & 7;
+    int found       = 0;
+    std::lock_guard<std::recursive_mutex> lock(g_rt.mu);
+    for (size_t off = lo; off + 8 <= closure_bytes && found < max_out; off += 8) {
+        char* word = nullptr;
+        memcpy(&word, p + off, 8);
+        if (!word) continue;
+        auto it = g_rt.allocs.find(word);
+        if (it == g_rt.allocs.end()) continue;
+        bool seen = false;
+        for (int k = 0; k < found; ++k) seen |= bases[k] == word;
+        if (seen) continue;
+        bases[found] = word;
+        bytes[found] = it->second->bytes;
+        ++found;
+    }
+    return found;
 }
 
 int sclx_b200_array_owner(const void* ptr) {

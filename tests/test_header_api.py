@@ -73,8 +73,11 @@ def run_dump(binary, case, n, path, emulate=None, real_devices=1):
     if emulate:
         env["SCLX_B200_EMULATE_DEVICES"] = str(emulate)
     env["CUDA_VISIBLE_DEVICES"] = ",".join(str(i) for i in range(real_devices))
-    if case.startswith("gather_x") and (emulate or real_devices > 1):
+    if case.startswith("gather_x"):
+        # the binned form on every device count (one device: regions of the same partition),
+        # with small regions so that even these sources span many buckets
         env["SCLX_GATHER_MODE"] = "exchange"
+        env["SCLX_B200_GATHER_REGION_KB"] = "64"
     p = subprocess.run([binary, "dump", case, str(n), path], capture_output=True, text=True, timeout=600, env=env)
     assert p.returncode == 0, f"{os.path.basename(binary)} {case}: rc={p.returncode}\n{p.stdout}\n{p.stderr}"
 
@@ -223,6 +226,25 @@ def test_driver_case_on_real_multi_gpu(binaries, oracle, tmp_path, case):
         theirs = str(tmp_path / "ref.bin")
         run_dump(ref, case, n, theirs, real_devices=ngpu)
         compare(got, np.fromfile(theirs, dtype=dtype), tol, f"{case}: ours vs reference UM build, {ngpu} GPUs")
+
+
+@pytest.mark.parametrize("emulate,n,region_kb", [(None, 1 << 22, None), (None, 1 << 24, 8192), (3, (1 << 22) + 5, 2048)])
+def test_binned_gather_selfcheck_large(binaries, tmp_path, emulate, n, region_kb):
+    """sclx::algorithm::gather (binned: partition / serve from L2-resident regions / place) against
+    the user-lambda gather on the device, at sizes where a source spans several real regions"""
+    ours, _ = binaries
+    env = dict(os.environ, CUDA_VISIBLE_DEVICES="0")
+    env.pop("SCLX_B200_EMULATE_DEVICES", None)
+    if emulate:
+        env["SCLX_B200_EMULATE_DEVICES"] = str(emulate)
+    if region_kb:
+        env["SCLX_B200_GATHER_REGION_KB"] = str(region_kb)
+    out = str(tmp_path / "check.bin")
+    p = subprocess.run([ours, "dump", "gather_x_selfcheck", str(n), out], capture_output=True, text=True,
+                       timeout=600, env=env)
+    assert p.returncode == 0, p.stderr[-2000:]
+    bad, count = np.fromfile(out, dtype=np.uint64)
+    assert (int(bad), int(count)) == (0, n)
 
 
 def run_example(name, emulate=None, timeout=900):

@@ -34,15 +34,19 @@ def main():
     ap.add_argument("--steps", type=int, default=200)
     ap.add_argument("--warmup", type=int, default=20)
     ap.add_argument("--out", default=None)
+    ap.add_argument("--emulate", type=int, default=0,
+                    help="ours only: N logical devices on GPU 0 (the host-side cost of N-device launch groups)")
     args = ap.parse_args()
-    table = {"n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup,
+    table = {"n_gpus": args.gpus, "emulated_devices": args.emulate, "steps": args.steps, "warmup": args.warmup,
              "timing": "wall clock around the blocking public API call, microseconds per step", "cases": []}
     for name, n, what in CASES:
         row = {"case": name, "n": n, "step": what}
         for tag, binary in (("ours_us", OURS), ("reference_um_us", REF)):
             if not os.path.exists(binary):
                 continue
-            r = run(binary, name, n, args.steps, args.warmup, args.gpus, 300)
+            if args.emulate and tag != "ours_us":
+                continue
+            r = run(binary, name, n, args.steps, args.warmup, args.gpus, 300, emulate=args.emulate)
             row[tag] = round(r["ms_per_step"] * 1e3, 2) if "ms_per_step" in r else r
         if isinstance(row.get("ours_us"), float) and isinstance(row.get("reference_um_us"), float):
             row["reference_over_ours"] = round(row["reference_um_us"] / row["ours_us"], 1)

@@ -34,11 +34,13 @@ def cases(n_gpus, scale):
     ]
 
 
-def run(binary, case, n, steps, warmup, n_gpus, timeout, extra_env=None):
+def run(binary, case, n, steps, warmup, n_gpus, timeout, extra_env=None, emulate=0):
     env = dict(os.environ)
     env.update(extra_env or {})
     env["CUDA_VISIBLE_DEVICES"] = ",".join(str(i) for i in range(n_gpus))
     env.pop("SCLX_B200_EMULATE_DEVICES", None)
+    if emulate:  # N logical devices on GPU 0: the host side of an N-device launch on one GPU
+        env["SCLX_B200_EMULATE_DEVICES"] = str(emulate)
     try:
         p = subprocess.run([binary, "bench", case, str(n), str(steps), str(warmup)], capture_output=True, text=True,
                            timeout=timeout, env=env)
