@@ -215,6 +215,7 @@ __host__ void gather(
 
             b200::gx_geometry_t geo;
             geo.div          = b200::gx_make_div(per);
+            geo.magic32      = per < (size_t(1) << 32) ? unsigned((size_t(1) << 32) / per) : 0u;
             geo.region_shift = region_shift;
             geo.regions      = regions;
             geo.buckets      = buckets;
@@ -268,8 +269,20 @@ __host__ void gather(
                 // one tile per CTA (staggered CTA starts de-synchronise the load / bucket / store
                 // phases of the chip; a single resident wave runs them in lock step)
                 const unsigned grid = unsigned(std::min<size_t>(tiles_r[p.ordinal], size_t(1) << 20));
-                b200::gx_partition_kernel<U, index_t_>
-                    <<<grid, b200::kGxThreads, 0, p.stream>>>(x, idx_ptr + p.offset);
+                auto launch_k1 = [&](auto kernel) {
+                    cuda::cuda_exception::raise_if_not_success(
+                        cudaFuncSetAttribute(
+                            kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, int(b200::kGxPartitionSmem)
+                        ),
+                        std::experimental::source_location::current(),
+                        "sclx::algorithm::"
+                    );
+                    kernel<<<grid, b200::kGxThreads, b200::kGxPartitionSmem, p.stream>>>(x, idx_ptr + p.offset);
+                };
+                if (nown == 1) launch_k1(b200::gx_partition_kernel<U, index_t_, b200::kGxOneOwner>);
+                else if (src.elements() <= (size_t(1) << 32) && per < (size_t(1) << 32))
+                    launch_k1(b200::gx_partition_kernel<U, index_t_, b200::kGxOwner32>);
+                else launch_k1(b200::gx_partition_kernel<U, index_t_, b200::kGxOwner64>);
             });
             b200::for_each_partition(src, src_info, [&](const b200::partition_t& p) {
                 unsigned max_cap = 0;

@@ -42,6 +42,7 @@ constexpr int kGxThreads      = 512;
 constexpr int kGxPerThread    = 8;
 constexpr int kGxTile         = kGxThreads * kGxPerThread;  // 4096 indices per tile
 constexpr unsigned kGxRunAlign = 8;   // queue runs start on 32-byte sectors
+constexpr size_t kGxPartitionSmem = size_t(kGxTile) * (sizeof(unsigned long long) + sizeof(unsigned));  // K1, dynamic
 
 // e / per and e % per with one 64x64 high multiply (per is the same for every partition but
 // the last: ceil(last/ndev) * leading elements)
@@ -71,6 +72,7 @@ gx_owner(unsigned long long e, const gx_div_t& d, unsigned& q, unsigned& off) {
 // owner's partition (2^region_shift elements each); bucket = q * regions + s
 struct gx_geometry_t {
     gx_div_t div;
+    unsigned magic32;  // floor(2^32 / per) when per < 2^32 (kGxOwner32)
     unsigned region_shift;
     unsigned regions;  // per owner
     unsigned buckets;  // nowners * regions
@@ -130,12 +132,37 @@ __device__ __forceinline__ void gx_scan_counts(const unsigned short* cnt, unsign
 // Per-thread state is packed (32-bit offset + bucket<<16|rank) so three 512-thread CTAs fit an
 // SM (profiles/r01_ncu_gather_exchange_details.txt: keeping the 64-bit indices live cost a CTA
 // per SM and made the kernel issue-bound).
-template<class U, class I>
+// how K1 finds the owner of a source element: compiled in, so the common cases carry no
+// 64-bit division code (47 instructions per index in the generic form)
+enum gx_owner_mode : int {
+    kGxOneOwner   = 0,  // a single partition: the element index IS the offset
+    kGxOwner32    = 1,  // several owners, fewer than 2^32 source elements: 32-bit magic division
+    kGxOwner64    = 2   // general
+};
+
+// e / per for e < 2^32: one 32x32 high multiply and a correction step
+__device__ __forceinline__ void gx_owner32(unsigned e, unsigned per, unsigned magic, unsigned& q, unsigned& off) {
+    unsigned qq = __umulhi(e, magic);
+    unsigned r  = e - qq * per;
+    if (r >= per) {
+        ++qq;
+        r -= per;
+    }
+    q   = qq;
+    off = r;
+}
+
+template<class U, class I, int OWNER_MODE>
 __global__ void __launch_bounds__(kGxThreads, 3)
     gx_partition_kernel(gx_requester_t<U> rq, const I* __restrict__ index) {
-    // one 64-bit record per queued index, in slot order: offset | bucket << 32 | position << 48
-    // (one shared-memory store when the tile is bucketed, one load when it is written out)
-    __shared__ unsigned long long s_rec[kGxTile];
+    // dynamic shared memory (kGxPartitionSmem bytes):
+    //   s_rec  one 64-bit record per queued index, in slot order: offset | bucket << 32 |
+    //          position << 48 (one store when the tile is bucketed, one load when it is written)
+    //   s_off  the offsets in index order between the two passes over the tile (keeping them in
+    //          registers across three barriers spilled to local memory)
+    extern __shared__ __align__(16) unsigned char s_dyn[];
+    unsigned long long* s_rec = reinterpret_cast<unsigned long long*>(s_dyn);
+    unsigned* s_off           = reinterpret_cast<unsigned*>(s_dyn + sizeof(unsigned long long) * kGxTile);
     __shared__ unsigned s_cnt[kGxMaxBuckets];
     __shared__ unsigned s_span[kGxMaxBuckets + 1];  // first slot | entries taken << 16, per bucket
     __shared__ unsigned s_start[kGxMaxBuckets + 1];
@@ -152,7 +179,7 @@ __global__ void __launch_bounds__(kGxThreads, 3)
         const size_t tbase   = t * kGxTile;
         const unsigned avail = unsigned(rq.n - tbase < size_t(kGxTile) ? rq.n - tbase : size_t(kGxTile));
         const I* __restrict__ tile_index = index + tbase;
-        unsigned off[kGxPerThread], br[kGxPerThread];  // br = bucket << 16 | rank in (tile, bucket)
+        unsigned br[kGxPerThread];  // bucket << 16 | rank in (tile, bucket)
         {
             unsigned long long e[kGxPerThread];
 #pragma unroll
@@ -163,17 +190,20 @@ __global__ void __launch_bounds__(kGxThreads, 3)
 #pragma unroll
             for (int k = 0; k < kGxPerThread; ++k) {
                 const bool valid = unsigned(k) * kGxThreads + tid < avail;
-                unsigned b       = 0xffffu;
-                off[k]           = 0;
+                unsigned b       = 0xffffu, off = 0;
                 if (valid) {
                     unsigned q = 0;
-                    if (rq.nowners == 1) off[k] = unsigned(e[k]);  // one owner: no division
-                    else gx_owner(e[k], rq.geo.div, q, off[k]);
-                    if (q >= unsigned(rq.nowners)) q = unsigned(rq.nowners) - 1;  // out of range: UB upstream too
-                    unsigned s = off[k] >> rq.geo.region_shift;
+                    if constexpr (OWNER_MODE == kGxOneOwner) off = unsigned(e[k]);
+                    else if constexpr (OWNER_MODE == kGxOwner32)
+                        gx_owner32(unsigned(e[k]), unsigned(rq.geo.div.per), rq.geo.magic32, q, off);
+                    else gx_owner(e[k], rq.geo.div, q, off);
+                    if (OWNER_MODE != kGxOneOwner && q >= unsigned(rq.nowners))
+                        q = unsigned(rq.nowners) - 1;  // out of range: UB upstream too
+                    unsigned s = off >> rq.geo.region_shift;
                     if (s >= regions) s = regions - 1;
                     b = q * regions + s;
                 }
+                s_off[unsigned(k) * kGxThreads + tid] = off;
                 // rank inside (tile, bucket): one shared-memory atomic per index.  With hundreds
                 // of buckets the lanes of a warp rarely collide; aggregating equal buckets with
                 // __match_any_sync first cost 3x the whole kernel (profiles/r02_ncu_gather_binned_v1.txt)
@@ -207,7 +237,7 @@ __global__ void __launch_bounds__(kGxThreads, 3)
                 const unsigned span = s_span[b];
                 if (rank < (span >> 16)) {
                     s_rec[(span & 0xffffu) + rank]
-                        = (unsigned long long)off[k] | ((unsigned long long)b << 32) | ((unsigned long long)j << 48);
+                        = (unsigned long long)s_off[j] | ((unsigned long long)b << 32) | ((unsigned long long)j << 48);
                 } else {
                     // queue full: direct (peer) load
                     rq.out[tbase + j] = rq.src_base[(unsigned long long)__ldg(tile_index + j)];
@@ -221,12 +251,14 @@ __global__ void __launch_bounds__(kGxThreads, 3)
             const unsigned long long rec = s_rec[i];
             const unsigned b    = unsigned(rec >> 32) & 0xffffu;
             const unsigned span = s_span[b];
-            const unsigned r = i - (span & 0xffffu), take = span >> 16;
-            unsigned* __restrict__ run = s_run[b];
-            run[r]                     = unsigned(rec);
-            if (r + 1 == take)  // the run's padding slots are served too: make them harmless
-                for (unsigned p = take; p < ((take + kGxRunAlign - 1u) & ~(kGxRunAlign - 1u)); ++p) run[p] = 0u;
-            rq.pos[tbase + i] = (unsigned short)(rec >> 48);
+            s_run[b][i - (span & 0xffffu)] = unsigned(rec);
+            rq.pos[tbase + i]              = (unsigned short)(rec >> 48);
+        }
+        // the padding slots of every run are served too: make them harmless (one thread per
+        // bucket; inside the loop above the branch made every warp walk the padding path)
+        for (unsigned b = tid; b < nb; b += kGxThreads) {
+            const unsigned take = s_take[b];
+            for (unsigned p = take; p < ((take + kGxRunAlign - 1u) & ~(kGxRunAlign - 1u)); ++p) s_run[b][p] = 0u;
         }
         __syncthreads();
     }
@@ -324,7 +356,6 @@ __global__ void __launch_bounds__(kGxThreads, 3) gx_place_kernel(gx_requester_t<
     __shared__ unsigned short s_take[kGxMaxBuckets], s_bkt[kGxTile];
     __shared__ unsigned s_written[kGxTile / 32];  // bit per window slot: value came through a queue
     const unsigned tid     = threadIdx.x;
-    const unsigned lane    = tid & 31, warp = tid >> 5;
     const unsigned nb      = rq.geo.buckets;
     const unsigned regions = rq.geo.regions;
     const size_t tiles     = (rq.n + kGxTile - 1) / kGxTile;
@@ -338,9 +369,11 @@ __global__ void __launch_bounds__(kGxThreads, 3) gx_place_kernel(gx_requester_t<
         __syncthreads();
         gx_scan_counts(s_take, s_start, int(nb));
         __syncthreads();
-        for (unsigned b = warp; b < nb; b += kGxThreads / 32) {
+        // slot -> bucket map: one thread per bucket stamps its run (a warp per bucket with a
+        // lane loop cost half of the kernel's instructions: profiles/r02_ncu_gather_binned_v4.txt)
+        for (unsigned b = tid; b < nb; b += kGxThreads) {
             const unsigned first = s_start[b], take = s_take[b];
-            for (unsigned j = lane; j < take; j += 32) s_bkt[first + j] = (unsigned short)b;
+            for (unsigned j = 0; j < take; ++j) s_bkt[first + j] = (unsigned short)b;
         }
         __syncthreads();
         const size_t tbase   = t * kGxTile;
