@@ -20,6 +20,8 @@
 #include "../execute_kernel.cuh"
 
 #include <algorithm>
+#include <chrono>
+#include <cstdio>
 #include <cstdlib>
 #include <mutex>
 #include <type_traits>
@@ -194,17 +196,26 @@ __host__ void gather(
             // offsets (filled in below once the bases are known)
             std::vector<std::vector<size_t>> queue_off(nreq, std::vector<size_t>(nown)),
                 resp_off(nreq, std::vector<size_t>(nown));
-            std::vector<size_t> counters_off(nreq), pos_off(nreq), tbase_off(nreq), tcnt_off(nreq);
+            std::vector<size_t> counters_off(nreq), pos_off(nreq), tbase_off(nreq), tcnt_off(nreq), done_off(nreq);
+            std::vector<std::vector<size_t>> pub_off(nreq, std::vector<size_t>(nown));
             for (int r = 0; r < nreq; ++r) {
                 const int rdev  = std::get<0>(out_info[r]);
                 counters_off[r] = reserve(rdev, sizeof(unsigned) * buckets);
                 pos_off[r]      = reserve(rdev, tiles_r[r] * b200::kGxTile * sizeof(unsigned short));
                 tbase_off[r]    = reserve(rdev, tiles_r[r] * buckets * sizeof(unsigned));
                 tcnt_off[r]     = reserve(rdev, tiles_r[r] * buckets * sizeof(unsigned short));
+                // Queues AND response buffers live in the requester's memory: K1 writes its
+                // queues locally, the owner's K2 pulls them in 4 KiB chunks and pushes the
+                // responses back in 4 KiB chunks (full NVLink lines both ways), K3 is local.
+                // Measured on 2 B200 (profiles/r02_gather_n2_push_vs_pull.txt): pushing the
+                // queue RUNS (~128 B each) into the owner's memory made K1 2.5x slower, pulling
+                // the response runs made K3 1.8x slower.
                 for (int q = 0; q < nown; ++q) {
                     resp_off[r][q]  = reserve(rdev, size_t(regions) * cap[r] * sizeof(U));
-                    queue_off[r][q] = reserve(std::get<0>(src_info[q]), size_t(regions) * cap[r] * sizeof(unsigned));
+                    queue_off[r][q] = reserve(rdev, size_t(regions) * cap[r] * sizeof(unsigned));
+                    pub_off[r][q]   = reserve(std::get<0>(src_info[q]), size_t(regions) * sizeof(unsigned));
                 }
+                done_off[r] = reserve(rdev, 256);
             }
             for (auto& d : devs) {
                 void* ptr = nullptr;
@@ -233,9 +244,11 @@ __host__ void gather(
                 x.pos          = reinterpret_cast<unsigned short*>(at(rdev, pos_off[r]));
                 x.tile_base    = reinterpret_cast<unsigned*>(at(rdev, tbase_off[r]));
                 x.tile_cnt     = reinterpret_cast<unsigned short*>(at(rdev, tcnt_off[r]));
+                x.ctas_done    = reinterpret_cast<unsigned*>(at(rdev, done_off[r]));
                 for (int q = 0; q < nown; ++q) {
-                    x.queue[q] = reinterpret_cast<unsigned*>(at(std::get<0>(src_info[q]), queue_off[r][q]));
-                    x.resp[q]  = reinterpret_cast<U*>(at(rdev, resp_off[r][q]));
+                    x.queue[q]        = reinterpret_cast<unsigned*>(at(rdev, queue_off[r][q]));
+                    x.resp[q]         = reinterpret_cast<U*>(at(rdev, resp_off[r][q]));
+                    x.counters_pub[q] = reinterpret_cast<unsigned*>(at(std::get<0>(src_info[q]), pub_off[r][q]));
                 }
             }
             std::vector<b200::gx_owner_t<U>> ow(nown);
@@ -248,7 +261,7 @@ __host__ void gather(
                 y.region_shift = region_shift;
                 for (int r = 0; r < nreq; ++r) {
                     y.queue[r]   = rq[r].queue[q];
-                    y.counter[r] = rq[r].counters + size_t(q) * regions;
+                    y.counter[r] = rq[r].counters_pub[q];
                     y.cap[r]     = cap[r];
                     y.resp[r]    = rq[r].resp[q];
                 }
@@ -257,12 +270,31 @@ __host__ void gather(
                 const char* e = std::getenv("SCLX_B200_GATHER_PREFETCH");
                 return e ? std::atoi(e) : 1;
             }();
+            // SCLX_B200_GATHER_TRACE=1: wait after every phase and print its wall time (tuning aid)
+            static const bool trace = std::getenv("SCLX_B200_GATHER_TRACE") != nullptr;
+            std::vector<int> all_devices = b200::devices_of(out_info);
+            for (int d : b200::devices_of(src_info))
+                if (std::find(all_devices.begin(), all_devices.end(), d) == all_devices.end()) all_devices.push_back(d);
+            auto phase_clock = std::chrono::steady_clock::now();
+            auto phase_done  = [&](const char* what) {
+                if (!trace) return;
+                b200::sync_devices(all_devices);
+                const auto now = std::chrono::steady_clock::now();
+                std::fprintf(stderr, "gather %-9s %8.3f ms\n", what,
+                             std::chrono::duration<double, std::milli>(now - phase_clock).count());
+                phase_clock = now;
+            };
             // ---- three launch groups --------------------------------------------------------
             b200::for_each_partition(out, out_info, [&](const b200::partition_t& p) {
                 const auto& x = rq[p.ordinal];
                 if (x.n == 0) return;
                 cuda::cuda_exception::raise_if_not_success(
                     cudaMemsetAsync(x.counters, 0, sizeof(unsigned) * buckets, p.stream),
+                    std::experimental::source_location::current(),
+                    "sclx::algorithm::"
+                );
+                cuda::cuda_exception::raise_if_not_success(
+                    cudaMemsetAsync(x.ctas_done, 0, sizeof(unsigned), p.stream),
                     std::experimental::source_location::current(),
                     "sclx::algorithm::"
                 );
@@ -284,6 +316,7 @@ __host__ void gather(
                     launch_k1(b200::gx_partition_kernel<U, index_t_, b200::kGxOwner32>);
                 else launch_k1(b200::gx_partition_kernel<U, index_t_, b200::kGxOwner64>);
             });
+            phase_done("partition");
             b200::for_each_partition(src, src_info, [&](const b200::partition_t& p) {
                 unsigned max_cap = 0;
                 for (int r = 0; r < nreq; ++r) max_cap = std::max(max_cap, cap[r]);
@@ -294,12 +327,14 @@ __host__ void gather(
                 b200::gx_serve_kernel<U>
                     <<<grid, b200::kGxServeThreads, 0, p.stream>>>(ow[p.ordinal], prefetch_mode);
             });
+            phase_done("serve");
             b200::for_each_partition(out, out_info, [&](const b200::partition_t& p) {
                 const auto& x = rq[p.ordinal];
                 if (x.n == 0) return;
                 const unsigned grid = unsigned(std::min<size_t>(tiles_r[p.ordinal], size_t(1) << 20));
                 b200::gx_place_kernel<U><<<grid, b200::kGxThreads, 0, p.stream>>>(x);
             });
+            phase_done("place");
         }
     }
     std::vector<int> devices = b200::devices_of(out_info);

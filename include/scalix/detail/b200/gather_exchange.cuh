@@ -89,6 +89,8 @@ struct gx_requester_t {
     U* resp[kGxMaxParts];          // [regions][cap] responses from owner q, local
     unsigned cap;                  // capacity of every bucket's queue (multiple of kGxRunAlign)
     unsigned* counters;            // [buckets] entries reserved so far, local
+    unsigned* counters_pub[kGxMaxParts];  // [regions] copy of owner q's share of `counters`, in q's memory
+    unsigned* ctas_done;           // local, zero-initialised, self-resetting
     unsigned short* pos;           // [tiles * kGxTile] in-tile positions of queued entries
     unsigned* tile_base;           // [tiles][buckets] first queue slot of the tile's run
     unsigned short* tile_cnt;      // [tiles][buckets] length of that run
@@ -101,7 +103,7 @@ struct gx_owner_t {
     int nreq;
     unsigned regions, region_shift;
     const unsigned* queue[kGxMaxParts];    // (r -> this owner): [regions][cap[r]] offsets, local
-    const unsigned* counter[kGxMaxParts];  // &counters_r[this owner's first bucket], in r's memory
+    const unsigned* counter[kGxMaxParts];  // [regions] fill levels of requester r's queues, published here by K1
     unsigned cap[kGxMaxParts];
     U* resp[kGxMaxParts];  // [regions][cap[r]] response buffer, in requester r's memory
 };
@@ -262,6 +264,21 @@ __global__ void __launch_bounds__(kGxThreads, 3)
         }
         __syncthreads();
     }
+    // The CTA that finishes last publishes the fill levels to the owners' memory: K2 then reads
+    // a LOCAL word per CTA.  (Reading the requester's counter across NVLink from each of K2's
+    // ~10^5 CTAs made the serve phase 2.8x slower per entry on two GPUs than on one.)
+    __shared__ bool s_last;
+    __threadfence();
+    __syncthreads();
+    if (tid == 0) s_last = atomicAdd(rq.ctas_done, 1u) == gridDim.x - 1;
+    __syncthreads();
+    if (!s_last) return;
+    __threadfence();
+    for (unsigned b = tid; b < nb; b += kGxThreads) {
+        const unsigned q = b / regions, sub = b - q * regions;
+        rq.counters_pub[q][sub] = __ldcg(rq.counters + b);
+    }
+    if (tid == 0) *rq.ctas_done = 0;
 }
 
 // ---- K2 -----------------------------------------------------------------------------------
