@@ -13,7 +13,8 @@
 //                               once) written to peer-visible scratch; pass B: the same scan
 //                               kernel on every partition, seeded on the device with the chained
 //                               totals of the partitions below it.  No host round trip, no
-//                               fix-up pass; ordering between A and B is by stream events.
+//                               fix-up pass; A and B are issued in one fork-join and ordered
+//                               across devices by stream events.
 //                               This path needs an associative AND commutative operator with a
 //                               known neutral element (the thrust functors of functional.cuh);
 //                               any other functor uses the reference's scan + chain + fix-up
@@ -91,18 +92,23 @@ __host__ void inclusive_scan(
             // pass A: totals of every partition but the last, into peer-visible scratch
             T* totals       = ws.scratch<T>(size_t(nparts));
             const T neutral = detail::neutral_element<functor_t, T>();
-            b200::for_each_partition(arr, device_info, [&](const b200::partition_t& p) {
-                if (p.ordinal + 1 < nparts)
-                    b200::launch_reduce<T, functor_t>(
-                        in + p.offset, p.elements, neutral, totals + p.ordinal, op, p, ws
+            // pass A (totals of every partition but the last) and pass B (the scan, seeded with
+            // the chained totals of the partitions below) in ONE fork-join: device d's stream
+            // waits for pass A of the devices below it between its two kernels
+            b200::for_each_partition_chained(
+                arr, device_info, /*lower_only=*/true,
+                [&](const b200::partition_t& p) {
+                    if (p.ordinal + 1 < nparts)
+                        b200::launch_reduce<T, functor_t>(
+                            in + p.offset, p.elements, neutral, totals + p.ordinal, op, p, ws
+                        );
+                },
+                [&](const b200::partition_t& p) {
+                    b200::launch_inclusive_scan<T, functor_t>(
+                        in + p.offset, out + p.offset, p.elements, totals, p.ordinal, nullptr, op, p, ws
                     );
-            });
-            // pass B (ordered after A on every device by the launch-group events)
-            b200::for_each_partition(arr, device_info, [&](const b200::partition_t& p) {
-                b200::launch_inclusive_scan<T, functor_t>(
-                    in + p.offset, out + p.offset, p.elements, totals, p.ordinal, nullptr, op, p, ws
-                );
-            });
+                }
+            );
         } else {
             // generic functor: the reference's three stages on top of the scan kernel
             T* lasts = ws.scratch<T>(size_t(nparts));

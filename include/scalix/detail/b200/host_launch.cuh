@@ -41,6 +41,25 @@ void for_each_partition(
     );
 }
 
+// two dependent kernels per partition in one fork-join (sclx::detail::run_chained_launch_groups)
+template<class T, uint Rank, class First, class Second>
+void for_each_partition_chained(
+    const array<T, Rank>& arr,
+    const sclx::detail::device_info_t& device_info,
+    bool lower_only,
+    First&& first,
+    Second&& second
+) {
+    const size_t last = arr.shape()[Rank - 1];
+    const size_t lead = last ? arr.elements() / last : 0;
+    auto wrap = [lead](auto& fn) {
+        return [&fn, lead](int ordinal, int device_id, size_t slice_idx, size_t slice_size, cudaStream_t stream) {
+            fn(partition_t{ordinal, device_id, slice_idx * lead, slice_size * lead, stream});
+        };
+    };
+    sclx::detail::run_chained_launch_groups(device_info, lower_only, wrap(first), wrap(second));
+}
+
 template<class T, uint Rank, class Fn>
 void for_each_partition(const array<T, Rank>& arr, Fn&& fn) {
     for_each_partition(arr, get_device_split_info(arr), std::forward<Fn>(fn));

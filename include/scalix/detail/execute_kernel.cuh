@@ -21,6 +21,7 @@
 #include "b200/dispatch.cuh"
 #include "b200/launch_config.cuh"
 
+#include <atomic>
 #include <cstdlib>
 #include <iostream>
 #include <mutex>
@@ -142,6 +143,84 @@ prefetch_plan_t make_prefetch_plan(const Functor& f, size_t range_elements) {
         plan.add(bases[k], unsigned(per));
     }
     return plan;
+}
+
+// Two launch groups in one: on every device `first` then `second`, where `second` on device i
+// must see what `first` produced on other devices (all of them, or only the partitions below
+// i when `lower_only`).  Issued as ONE fork-join: each device's thread queues its first kernel,
+// records its event, meets the others at a host-side barrier (all events recorded), makes its
+// stream wait for the events it needs and queues its second kernel.  Two plain groups would
+// pay the hand-over twice and serialise ~3N event calls on the calling thread in between.
+template<class First, class Second>
+void run_chained_launch_groups(
+    const device_info_t& device_info, bool lower_only, First&& first, Second&& second
+) {
+    const int n = int(device_info.size());
+    bool distinct = true;
+    for (int i = 0; i < n; ++i)
+        for (int j = 0; j < i; ++j) distinct &= std::get<0>(device_info[i]) != std::get<0>(device_info[j]);
+    if (n == 1 || !distinct) {
+        // one stream orders the two kernels by itself / a device listed twice would meet itself
+        // at the barrier: plain groups
+        run_launch_group(device_info, first);
+        run_launch_group(device_info, second);
+        return;
+    }
+    cuda::detail::ensure_runtime();
+    std::vector<int> devices(n);
+    for (int i = 0; i < n; ++i) devices[i] = std::get<0>(device_info[i]);
+    cuda::detail::check_rt(sclx_b200_rt_begin_launch(n, devices.data()));
+    const int caller_device = cuda::traits::current_device();
+    auto issue = [&](auto& what, int ordinal) {
+        const auto& [device_id, slice_idx, slice_size] = device_info[ordinal];
+        cuda::set_device(device_id);
+        what(ordinal, device_id, slice_idx, slice_size, static_cast<cudaStream_t>(sclx_b200_rt_stream(device_id)));
+        cuda::cuda_exception::raise_if_not_success(
+            cudaGetLastError(), std::experimental::source_location::current(), "sclx::detail::"
+        );
+    };
+    auto wait_for_others = [&](int ordinal) {
+        for (int j = 0; j < (lower_only ? ordinal : n); ++j)
+            if (j != ordinal) cuda::detail::check_rt(sclx_b200_rt_wait_done(devices[ordinal], devices[j]));
+    };
+    if (n <= inline_issue_limit) {
+        for (int i = 0; i < n; ++i) {
+            issue(first, i);
+            cuda::detail::check_rt(sclx_b200_rt_record_done(devices[i]));
+        }
+        for (int i = 0; i < n; ++i) {
+            wait_for_others(i);
+            issue(second, i);
+        }
+    } else {
+        std::atomic<int> arrived{0};
+        std::atomic<bool> failed{false};
+        cuda::detail::device_workers::instance().run_on(devices.data(), n, [&](int i) {
+            std::exception_ptr error;
+            try {
+                issue(first, i);
+                cuda::detail::check_rt(sclx_b200_rt_record_done(devices[i]));
+            } catch (...) {
+                error = std::current_exception();
+                failed.store(true);
+            }
+            // every device's event is recorded before anybody waits for one
+            arrived.fetch_add(1, std::memory_order_acq_rel);
+            while (arrived.load(std::memory_order_acquire) < n) {
+#if defined(__x86_64__)
+                __builtin_ia32_pause();
+#endif
+            }
+            if (error) std::rethrow_exception(error);
+            if (failed.load()) return;
+            wait_for_others(i);
+            issue(second, i);
+        });
+    }
+    cuda::set_device(caller_device);
+    cuda::detail::check_rt(sclx_b200_rt_end_launch(n, devices.data()));
+    sclx_b200_note_launches(static_cast<unsigned long long>(2 * n));
+    for (int d : devices) launch_record::note(d);
 }
 
 template<class Kernel>

@@ -210,6 +210,9 @@ unsigned long long sclx_b200_rt_host_faults(void);
 int sclx_b200_rt_begin_launch(int ndev, const int* devices);
 int sclx_b200_rt_end_launch(int ndev, const int* devices);
 int sclx_b200_rt_stream_wait(int waiter, int signaller);
+/* record `logical`'s event on its stream / make `waiter`'s stream wait for `signaller`'s event */
+int sclx_b200_rt_record_done(int logical);
+int sclx_b200_rt_wait_done(int waiter, int signaller);
 int sclx_b200_rt_sync_devices(int ndev, const int* devices);
 int sclx_b200_rt_devices_idle(int ndev, const int* devices); /* 1 = nothing running (never blocks) */
 

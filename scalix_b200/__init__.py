@@ -82,6 +82,8 @@ ABI = {
     "sclx_b200_rt_begin_launch": (_i, [_i, _vp]),
     "sclx_b200_rt_end_launch": (_i, [_i, _vp]),
     "sclx_b200_rt_stream_wait": (_i, [_i, _i]),
+    "sclx_b200_rt_record_done": (_i, [_i]),
+    "sclx_b200_rt_wait_done": (_i, [_i, _i]),
     "sclx_b200_rt_sync_devices": (_i, [_i, _vp]),
     "sclx_b200_rt_devices_idle": (_i, [_i, _vp]),
     "sclx_b200_rt_workspace_acquire": (_i, [_i, _pp]),

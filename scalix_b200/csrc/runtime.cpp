@@ -981,6 +981,23 @@ int sclx_b200_rt_stream_wait(int waiter, int signaller) {
     return 0;
 }
 
+// the two halves of sclx_b200_rt_stream_wait, for launch groups whose second kernel on device i
+// depends on the FIRST kernel of other devices (chained groups, detail/execute_kernel.cuh): every
+// device's issuing thread records its own event, then waits for the others'.  No lock: each
+// call touches one device's event, and the callers order records before waits themselves.
+int sclx_b200_rt_record_done(int logical) {
+    if (logical < 0 || logical >= (int)g_rt.dev.size()) return fail(SCLX_E_INVALID_ARGUMENT, "record_done: bad device");
+    RT(cudaEventRecord(g_rt.dev[logical].done, g_rt.dev[logical].stream));
+    return 0;
+}
+int sclx_b200_rt_wait_done(int waiter, int signaller) {
+    if (waiter < 0 || signaller < 0 || waiter >= (int)g_rt.dev.size() || signaller >= (int)g_rt.dev.size())
+        return fail(SCLX_E_INVALID_ARGUMENT, "wait_done: bad device");
+    if (waiter == signaller) return 0;
+    RT(cudaStreamWaitEvent(g_rt.dev[waiter].stream, g_rt.dev[signaller].done, 0));
+    return 0;
+}
+
 int sclx_b200_rt_sync_devices(int ndev, const int* devices) {
     if (int rc = ensure_init()) return rc;
     const int total = (int)g_rt.dev.size();
