@@ -344,7 +344,9 @@ class device_workers {
 
     static long poll_microseconds() {
         if (const char* e = std::getenv("SCLX_B200_WORKER_SPIN_US")) return std::atol(e);
-        return 200;
+        // long enough to bridge one large kernel between two launch groups of a loop (a 4 GiB
+        // reduce_last_dim step is 0.6 ms): the next group then finds the workers awake
+        return 2000;
     }
 
     explicit device_workers(int count) {
