@@ -231,7 +231,8 @@ def test_driver_case_on_real_multi_gpu(binaries, oracle, tmp_path, case):
         compare(got, np.fromfile(theirs, dtype=dtype), tol, f"{case}: ours vs reference UM build, {ngpu} GPUs")
 
 
-@pytest.mark.parametrize("emulate,n,region_kb", [(None, 1 << 22, None), (None, 1 << 24, 8192), (3, (1 << 22) + 5, 2048)])
+@pytest.mark.parametrize("emulate,n,region_kb", [(None, 1 << 22, None), (None, 1 << 24, 8192), (3, (1 << 22) + 5, 2048),
+                                                 (None, 1 << 28, None)])  # the last one is BASELINE config 4 at full size
 def test_binned_gather_selfcheck_large(binaries, tmp_path, emulate, n, region_kb):
     """sclx::algorithm::gather (binned: partition / serve from L2-resident regions / place) against
     the user-lambda gather on the device, at sizes where a source spans several real regions"""
