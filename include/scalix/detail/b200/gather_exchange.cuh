@@ -305,7 +305,7 @@ __device__ __forceinline__ void gx_prefetch_l2(const void* begin, const void* en
     asm volatile("cp.async.bulk.prefetch.L2.global [%0], %1;" ::"l"(a0), "r"(unsigned(a1 - a0)) : "memory");
 }
 
-constexpr int kGxServeThreads = 256, kGxServeUnroll = 4;
+constexpr int kGxServeThreads = 256, kGxServeUnroll = 8;
 constexpr int kGxServeChunk   = kGxServeThreads * kGxServeUnroll;
 
 // grid = (ceil(max cap / chunk), nreq, regions): CTA (x, r, s) serves entries
