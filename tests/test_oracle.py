@@ -170,3 +170,22 @@ def test_oracle_matches_outputs_of_the_reference_build(oracle, case, n, path):
     assert want is not None, case
     got = np.fromfile(path, dtype=dtype)
     compare(got, want, tol, f"{case} n={n}: reference build output vs CPU oracle")
+
+
+def test_bench_closed_forms_use_the_oracle_generator(oracle):
+    """bench.py checks the driver's results on the N devices it is about to time against closed
+    forms it computes itself with numpy (it may not execute oracle/ outside its CPU-baseline
+    leg): its generator must be the oracle's, value for value."""
+    import importlib.util
+    import os
+
+    spec = importlib.util.spec_from_file_location(
+        "_bench", os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "bench.py"))
+    bench = importlib.util.module_from_spec(spec)
+    spec.loader.exec_module(bench)
+    n = 10_007
+    want = np.array([oracle.lib.oracle_splitmix64(0x5CA5, i) for i in range(n)], dtype=np.uint64)
+    assert np.array_equal(bench.splitmix64(0x5CA5, np.arange(n, dtype=np.uint64)), want)
+    assert np.array_equal(bench.uniform01(0x5CA11, n).view(np.uint32), oracle.uniform_f32(n, 0x5CA11).view(np.uint32))
+    assert np.array_equal((bench.splitmix64(0x6A7, np.arange(n, dtype=np.uint64)) % np.uint64(4 * n)),
+                          oracle.index_u64(n, 0x6A7, 4 * n))
