@@ -83,7 +83,14 @@ struct launch_record {
 using device_info_t = std::vector<std::tuple<int, size_t, size_t>>;
 
 // launch groups of at most this many devices are queued by the calling thread itself
-constexpr int inline_issue_limit = 2;
+// (SCLX_B200_INLINE_ISSUE overrides)
+inline int inline_issue_limit() {
+    static const int limit = [] {
+        const char* e = std::getenv("SCLX_B200_INLINE_ISSUE");
+        return e ? std::atoi(e) : 2;
+    }();
+    return limit;
+}
 
 // `issue(ordinal, device_id, slice_idx, slice_size, stream)` queues one kernel; called with
 // the device current: inline for small groups, on the devices' persistent threads otherwise
@@ -105,7 +112,7 @@ void run_launch_group(const device_info_t& device_info, Issue&& issue) {
             cudaGetLastError(), std::experimental::source_location::current(), "sclx::detail::"
         );
     };
-    if (n <= inline_issue_limit) {
+    if (n <= inline_issue_limit()) {
         // one or two kernels are queued faster from here than a hand-over costs
         for (int i = 0; i < n; ++i) issue_one(i);
     } else {
@@ -183,7 +190,7 @@ void run_chained_launch_groups(
         for (int j = 0; j < (lower_only ? ordinal : n); ++j)
             if (j != ordinal) cuda::detail::check_rt(sclx_b200_rt_wait_done(devices[ordinal], devices[j]));
     };
-    if (n <= inline_issue_limit) {
+    if (n <= inline_issue_limit()) {
         for (int i = 0; i < n; ++i) {
             issue(first, i);
             cuda::detail::check_rt(sclx_b200_rt_record_done(devices[i]));
