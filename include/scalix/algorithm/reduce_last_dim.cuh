@@ -102,6 +102,16 @@ __host__ void reduce_last_dim(
             xchg.arrivals  = reinterpret_cast<unsigned*>(block + row_bytes);
             xchg.final_out = out;
             xchg.nparts    = nparts;
+            // the partition that folds last also tells the host: one polled word of pinned host
+            // memory instead of N stream synchronisations in a row
+            struct flag_lease {
+                unsigned* flag = nullptr;
+                ~flag_lease() { sclx_b200_rt_host_flag_release(flag); }
+            } done;
+            unsigned ticket = 0;
+            cuda::detail::check_rt(sclx_b200_rt_host_flag_acquire(&done.flag, &ticket));
+            xchg.done_flag   = done.flag;
+            xchg.done_ticket = ticket;
             b200::for_each_partition(arr, device_info, [&](const b200::partition_t& p) {
                 b200::row_exchange_t mine = xchg;
                 mine.ordinal              = p.ordinal;
@@ -110,7 +120,11 @@ __host__ void reduce_last_dim(
                 );
             });
             auto devices = b200::devices_of(device_info);
-            b200::sync_devices(devices);
+            if (rows > 0 && arr.elements() > 0)
+                cuda::detail::check_rt(
+                    sclx_b200_rt_host_flag_wait(done.flag, ticket, int(devices.size()), devices.data())
+                );
+            else b200::sync_devices(devices);
         }
     } else {
         array<T, Rank - 1> tmp(result_shape);

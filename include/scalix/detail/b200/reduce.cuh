@@ -59,6 +59,10 @@ struct row_exchange_t {
     void* final_out    = nullptr;  // rows values, peer-visible
     int nparts         = 0;
     int ordinal        = 0;
+    // optional: pinned, mapped host word that receives `done_ticket` once `final_out` is
+    // written — the caller polls it instead of synchronising every device's stream
+    unsigned* done_flag  = nullptr;
+    unsigned done_ticket = 0;
 };
 
 // ---------------------------------------------------------------------------
@@ -315,6 +319,11 @@ __global__ void __launch_bounds__(THREADS) reduce_last_dim_kernel(
         T a = identity;
         for (int q = 0; q < xchg.nparts; ++q) a = op(a, load_cg(all + size_t(q) * rows + r));
         final_out[r] = a;
+    }
+    if (xchg.done_flag != nullptr) {
+        __threadfence_system();
+        __syncthreads();
+        if (tid == 0) *reinterpret_cast<volatile unsigned*>(xchg.done_flag) = xchg.done_ticket;
     }
 }
 

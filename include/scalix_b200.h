@@ -215,6 +215,12 @@ int sclx_b200_rt_record_done(int logical);
 int sclx_b200_rt_wait_done(int waiter, int signaller);
 int sclx_b200_rt_sync_devices(int ndev, const int* devices);
 int sclx_b200_rt_devices_idle(int ndev, const int* devices); /* 1 = nothing running (never blocks) */
+/* host-polled completion: a word of pinned, mapped host memory + a process-wide ticket; the
+ * kernel that finishes a multi-device operation stores the ticket, the caller polls for it
+ * instead of synchronising N streams (errors fall back to a real synchronisation) */
+int sclx_b200_rt_host_flag_acquire(unsigned** flag, unsigned* ticket);
+int sclx_b200_rt_host_flag_release(unsigned* flag);
+int sclx_b200_rt_host_flag_wait(const unsigned* flag, unsigned ticket, int ndev, const int* devices);
 
 /* Workspaces of the scan / reduce kernels, LEASED PER CALL: one lease per (algorithm call,
  * logical device), used in stream order on that device's stream and returned when the call has

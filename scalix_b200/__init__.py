@@ -86,6 +86,9 @@ ABI = {
     "sclx_b200_rt_wait_done": (_i, [_i, _i]),
     "sclx_b200_rt_sync_devices": (_i, [_i, _vp]),
     "sclx_b200_rt_devices_idle": (_i, [_i, _vp]),
+    "sclx_b200_rt_host_flag_acquire": (_i, [_pp, _vp]),
+    "sclx_b200_rt_host_flag_release": (_i, [_vp]),
+    "sclx_b200_rt_host_flag_wait": (_i, [_vp, C.c_uint, _i, _vp]),
     "sclx_b200_rt_workspace_acquire": (_i, [_i, _pp]),
     "sclx_b200_rt_workspace_release": (_i, [_vp, _i]),
     "sclx_b200_rt_workspace_reduce": (_i, [_vp, _sz, _pp, _pp]),

@@ -1028,6 +1028,88 @@ int sclx_b200_rt_sync_devices(int ndev, const int* devices) {
     return 0;
 }
 
+// ---- host-polled completion ------------------------------------------------------------------
+// A kernel that KNOWS it is the last piece of a multi-device operation (the partition that
+// arrives last in reduce_last_dim's fused fold) stores a ticket into a word of pinned, mapped
+// host memory; the caller polls that word instead of synchronising N streams one after the
+// other.  Flags are leased per call; the value is a process-wide ticket, so a stale flag can
+// never satisfy a later wait.
+namespace {
+struct host_flag_pool {
+    std::mutex mu;
+    std::vector<unsigned*> free_flags;
+    std::atomic<unsigned> ticket{0};
+} g_flags;
+}  // namespace
+
+int sclx_b200_rt_host_flag_acquire(unsigned** flag, unsigned* ticket) {
+    if (int rc = ensure_init()) return rc;
+    if (!flag || !ticket) return fail(SCLX_E_INVALID_ARGUMENT, "host_flag_acquire: null out pointer");
+    {
+        std::lock_guard<std::mutex> lock(g_flags.mu);
+        if (!g_flags.free_flags.empty()) {
+            *flag = g_flags.free_flags.back();
+            g_flags.free_flags.pop_back();
+        } else {
+            void* block = nullptr;  // 64 flags at a time, one cache line each
+            RT(cudaHostAlloc(&block, 64 * 64, cudaHostAllocPortable | cudaHostAllocMapped));
+            memset(block, 0, 64 * 64);
+            for (int i = 1; i < 64; ++i) g_flags.free_flags.push_back(reinterpret_cast<unsigned*>((char*)block + 64 * i));
+            *flag = reinterpret_cast<unsigned*>(block);
+        }
+    }
+    unsigned t = g_flags.ticket.fetch_add(1) + 1;
+    if (t == 0) t = g_flags.ticket.fetch_add(1) + 1;  // 0 is "never signalled"
+    *ticket = t;
+    return 0;
+}
+
+int sclx_b200_rt_host_flag_release(unsigned* flag) {
+    if (!flag) return 0;
+    std::lock_guard<std::mutex> lock(g_flags.mu);
+    g_flags.free_flags.push_back(flag);
+    return 0;
+}
+
+// Wait until *flag == ticket.  The devices' streams are checked now and then: a launch or
+// execution error, or streams that went idle without the flag being set, end the wait with a
+// real synchronisation (which reports the error).  On success the devices count as
+// synchronised: everything the operation wrote was written before the flag.
+int sclx_b200_rt_host_flag_wait(const unsigned* flag, unsigned ticket, int ndev, const int* devices) {
+    if (int rc = ensure_init()) return rc;
+    const volatile unsigned* f       = flag;
+    const unsigned long long seq     = g_rt.launch_seq.load();
+    const int total                  = (int)g_rt.dev.size();
+    unsigned long long spins         = 0;
+    while (*f != ticket) {
+        if ((++spins & 0x3fff) == 0) {
+            bool all_idle = true, failed = false;
+            for (int i = 0; i < ndev; ++i) {
+                if (devices[i] < 0 || devices[i] >= total) continue;
+                cudaError_t e = cudaStreamQuery(g_rt.dev[devices[i]].stream);
+                if (e == cudaErrorNotReady) all_idle = false;
+                else if (e != cudaSuccess) failed = true;
+            }
+            if (failed || (all_idle && *f != ticket)) return sclx_b200_rt_sync_devices(ndev, devices);
+        }
+#if defined(__x86_64__)
+        __builtin_ia32_pause();
+#endif
+    }
+    unsigned long long seen = 0;
+    for (int i = 0; i < ndev; ++i)
+        if (devices[i] >= 0 && devices[i] < total && devices[i] < 64) seen |= 1ull << devices[i];
+    int distinct = 0;
+    for (int d = 0; d < total && d < 64; ++d) distinct += int(seen >> d & 1);
+    if (distinct == total) note_synced(seq);
+    else {
+        std::lock_guard<std::recursive_mutex> lock(g_rt.mu);
+        for (int d = 0; d < total && d < 64; ++d)
+            if ((seen >> d & 1) && g_rt.dev[d].host_synced_seq < seq) g_rt.dev[d].host_synced_seq = seq;
+    }
+    return 0;
+}
+
 // 1 when every stream in the list is idle, 0 when work is still running (never blocks)
 int sclx_b200_rt_devices_idle(int ndev, const int* devices) {
     if (ensure_init()) return 0;
