@@ -111,6 +111,7 @@ void run_launch_group(const device_info_t& device_info, Issue&& issue) {
         cuda::cuda_exception::raise_if_not_success(
             cudaGetLastError(), std::experimental::source_location::current(), "sclx::detail::"
         );
+        cuda::detail::check_rt(sclx_b200_rt_signal_done(device_id));  // what waits poll for
     };
     if (n <= inline_issue_limit()) {
         // one or two kernels are queued faster from here than a hand-over costs
@@ -198,6 +199,7 @@ void run_chained_launch_groups(
         for (int i = 0; i < n; ++i) {
             wait_for_others(i);
             issue(second, i);
+            cuda::detail::check_rt(sclx_b200_rt_signal_done(devices[i]));
         }
     } else {
         std::atomic<int> arrived{0};
@@ -222,6 +224,7 @@ void run_chained_launch_groups(
             if (failed.load()) return;
             wait_for_others(i);
             issue(second, i);
+            cuda::detail::check_rt(sclx_b200_rt_signal_done(devices[i]));
         });
     }
     cuda::set_device(caller_device);

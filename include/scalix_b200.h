@@ -213,6 +213,10 @@ int sclx_b200_rt_stream_wait(int waiter, int signaller);
 /* record `logical`'s event on its stream / make `waiter`'s stream wait for `signaller`'s event */
 int sclx_b200_rt_record_done(int logical);
 int sclx_b200_rt_wait_done(int waiter, int signaller);
+/* queue `logical`'s next completion ticket (a 32-bit stream write into pinned host memory)
+ * behind everything issued on its stream so far: sync_devices polls these words instead of
+ * calling cudaStreamSynchronize per device.  Every launch group ends with it. */
+int sclx_b200_rt_signal_done(int logical);
 int sclx_b200_rt_sync_devices(int ndev, const int* devices);
 int sclx_b200_rt_devices_idle(int ndev, const int* devices); /* 1 = nothing running (never blocks) */
 /* host-polled completion: a word of pinned, mapped host memory + a process-wide ticket; the

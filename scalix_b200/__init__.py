@@ -84,6 +84,7 @@ ABI = {
     "sclx_b200_rt_stream_wait": (_i, [_i, _i]),
     "sclx_b200_rt_record_done": (_i, [_i]),
     "sclx_b200_rt_wait_done": (_i, [_i, _i]),
+    "sclx_b200_rt_signal_done": (_i, [_i]),
     "sclx_b200_rt_sync_devices": (_i, [_i, _vp]),
     "sclx_b200_rt_devices_idle": (_i, [_i, _vp]),
     "sclx_b200_rt_host_flag_acquire": (_i, [_pp, _vp]),
