@@ -167,6 +167,26 @@ int sclx_b200_reduce_last_dim_host(const void* host_in, size_t rows, size_t cols
 int sclx_b200_inclusive_scan_host(const void* host_in, void* host_out, size_t n, int dtype,
                                   int op);
 
+/* ---- allocation-free variant -----------------------------------------------------------------
+ * NO COUNTERPART IN THE REFERENCE: added for callers
+ * that cannot call cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses
+ * that forbid it).  Same kernel, launch geometry and result bits as sclx_b200_reduce_last_dim,
+ * but the kernel's scratch (per-CTA partial rows + ticket) is a file-scope static __device__
+ * array of 2 MiB + 256 bytes (scalix_b200/csrc/no_alloc.cu) instead of a cudaMalloc'd workspace:
+ * the call allocates and frees nothing (it issues one 4-byte cudaMemsetAsync and one kernel on
+ * `stream`).  Every GPU that loads the library holds the array until the process exits.
+ *   - Limit: rows * sizeof(element) <= sclx_b200_noalloc_max_row_bytes() = 2048 bytes (512
+ *     4-byte or 256 8-byte rows); larger problems are rejected with SCLX_E_INVALID_ARGUMENT and a
+ *     message naming the limit.  `cols` is unlimited.
+ *   - All calls on a device SHARE the one array and it keeps the last call's contents (the call
+ *     clears the ticket word itself): calls that overlap on the GPU — different streams with no
+ *     ordering between them — race.  Calls on one stream, or ordered by events, are fine.
+ *   - The first call on a device resolves the array's device address (cudaGetSymbolAddress);
+ *     make one warm-up call per device before starting a graph capture. */
+size_t sclx_b200_noalloc_max_row_bytes(void);
+int sclx_b200_reduce_last_dim_noalloc(const void* in, size_t rows, size_t cols, int dtype, int op,
+                                      const void* identity, void* out, void* stream);
+
 /* ---- runtime under the sclx:: header API (include/scalix/) --------------------------------------
  * Logical devices are the physical GPUs, or N emulated devices on GPU 0 when
  * SCLX_B200_EMULATE_DEVICES=N / sclx_b200_rt_set_emulated_devices(N) is set before first use

@@ -60,6 +60,8 @@ ABI = {
     "sclx_b200_axpy_f32_rank3": (_i, [C.c_float, _vp, _vp, _sz, _sz, _sz, _i, _vp]),
     "sclx_b200_gather_launch_f32": (_i, [_vp, _sz, _vp, _vp, _i, _vp]),
     "sclx_b200_reduce_last_dim_host": (_i, [_vp, _sz, _sz, _i, _i, _vp, _vp]),
+    "sclx_b200_noalloc_max_row_bytes": (_sz, []),
+    "sclx_b200_reduce_last_dim_noalloc": (_i, [_vp, _sz, _sz, _i, _i, _vp, _vp, _vp]),
     "sclx_b200_inclusive_scan_host": (_i, [_vp, _vp, _sz, _i, _i]),
     "sclx_b200_launch_count": (C.c_ulonglong, []),
     "sclx_b200_note_launches": (C.c_ulonglong, [C.c_ulonglong]),

@@ -8,7 +8,7 @@ REPO = os.path.dirname(HERE)
 LIB_DIR = os.path.join(HERE, "lib")
 LIB = os.path.join(LIB_DIR, "libscalix_b200.so")
 OBJ_DIR = os.path.join(REPO, "build", "obj")
-SOURCES = ["scalix_b200.cu", "launch_instances.cu", "runtime.cpp"]
+SOURCES = ["scalix_b200.cu", "launch_instances.cu", "no_alloc.cu", "runtime.cpp"]
 NVCC_FLAGS = [
     "-std=c++17", "-O3", "-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo",
     "--extended-lambda", "--expt-relaxed-constexpr", "-Xcompiler", "-fPIC",
