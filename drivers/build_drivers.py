@@ -1,5 +1,6 @@
 """Builds the header-API programs against include/ (sm_100a) into drivers/bin/:
    parity_driver_ours  — drivers/parity_driver.cu (public sclx:: API only)
+   parity_driver_ours_checked — the same with -DSCLX_GX_CHECKS (bounds checks in the gather kernels)
    ex_<name>           — the reference's five examples, compiled UNMODIFIED from
                          /root/reference/examples (only when that tree is present; nothing is
                          copied into this repository, the binaries are git-ignored)
@@ -50,7 +51,10 @@ def main(force=False):
     # optional serialize case of the driver needs it
     cereal = "/root/reference/extern/cereal/include"
     extra = ("-I", cereal) if os.path.isdir(cereal) else ()
-    jobs = [(os.path.join(HERE, "parity_driver.cu"), os.path.join(BIN, "parity_driver_ours"), extra)]
+    jobs = [(os.path.join(HERE, "parity_driver.cu"), os.path.join(BIN, "parity_driver_ours"), extra),
+            # the same driver with bounds checks compiled into the gather kernels (SCLX_GX_CHECKS)
+            (os.path.join(HERE, "parity_driver.cu"), os.path.join(BIN, "parity_driver_ours_checked"),
+             (*extra, "-DSCLX_GX_CHECKS"))]
     if os.path.isdir(REF_EXAMPLES):
         for ex in EXAMPLES:
             jobs.append((os.path.join(REF_EXAMPLES, ex + ".cu"), os.path.join(BIN, "ex_" + ex),

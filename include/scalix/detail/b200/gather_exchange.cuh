@@ -33,6 +33,23 @@
 #include "primitives.cuh"
 
 #include <cstdint>
+#include <cstdio>
+
+// -DSCLX_GX_CHECKS: bounds checks on every queue / response / shared-memory index of the three
+// kernels; a violation traps the kernel (the launch then fails with an error instead of
+// corrupting memory).  compute-sanitizer is closed on the pool this was developed on, so the
+// gather tests are also run against a driver built with this switch (tests/test_header_api.py).
+#ifdef SCLX_GX_CHECKS
+#define SCLX_GX_ASSERT(cond)                                                                     \
+    do {                                                                                         \
+        if (!(cond)) {                                                                           \
+            printf("gather_exchange.cuh:%d: check failed: %s\n", __LINE__, #cond);               \
+            __trap();                                                                            \
+        }                                                                                        \
+    } while (0)
+#else
+#define SCLX_GX_ASSERT(cond) ((void)0)
+#endif
 
 namespace sclx::b200 {
 
@@ -238,6 +255,7 @@ __global__ void __launch_bounds__(kGxThreads, 3)
                 const unsigned b = br[k] >> 16, rank = br[k] & 0xffffu;
                 const unsigned span = s_span[b];
                 if (rank < (span >> 16)) {
+                    SCLX_GX_ASSERT((span & 0xffffu) + rank < unsigned(kGxTile));
                     s_rec[(span & 0xffffu) + rank]
                         = (unsigned long long)s_off[j] | ((unsigned long long)b << 32) | ((unsigned long long)j << 48);
                 } else {
@@ -253,6 +271,8 @@ __global__ void __launch_bounds__(kGxThreads, 3)
             const unsigned long long rec = s_rec[i];
             const unsigned b    = unsigned(rec >> 32) & 0xffffu;
             const unsigned span = s_span[b];
+            SCLX_GX_ASSERT(b < nb && i >= (span & 0xffffu) && i - (span & 0xffffu) < (span >> 16));
+            SCLX_GX_ASSERT(rq.tile_base[t * nb + b] + (i - (span & 0xffffu)) < rq.cap);
             s_run[b][i - (span & 0xffffu)] = unsigned(rec);
             rq.pos[tbase + i]              = (unsigned short)(rec >> 48);
         }
@@ -260,6 +280,7 @@ __global__ void __launch_bounds__(kGxThreads, 3)
         // bucket; inside the loop above the branch made every warp walk the padding path)
         for (unsigned b = tid; b < nb; b += kGxThreads) {
             const unsigned take = s_take[b];
+            SCLX_GX_ASSERT(take == 0 || rq.tile_base[t * nb + b] + ((take + kGxRunAlign - 1u) & ~(kGxRunAlign - 1u)) <= rq.cap);
             for (unsigned p = take; p < ((take + kGxRunAlign - 1u) & ~(kGxRunAlign - 1u)); ++p) s_run[b][p] = 0u;
         }
         __syncthreads();
@@ -349,7 +370,13 @@ __global__ void __launch_bounds__(kGxServeThreads) gx_serve_kernel(gx_owner_t<U>
         o[u]             = i < left ? __ldcs(queue + i) : 0u;
     }
 #pragma unroll
-    for (int u = 0; u < kGxServeUnroll; ++u) v[u] = gx_load_random(ow.src_local + o[u]);
+    for (int u = 0; u < kGxServeUnroll; ++u) {
+        SCLX_GX_ASSERT(size_t(o[u]) < ow.part_elems);
+        SCLX_GX_ASSERT(unsigned(u) * kGxServeThreads + threadIdx.x >= left
+                       || (size_t(o[u]) >> ow.region_shift) == s || (s + 1 == ow.regions && (size_t(o[u]) >> ow.region_shift) >= s)
+                       || o[u] == 0u);
+        v[u] = gx_load_random(ow.src_local + o[u]);
+    }
 #pragma unroll
     for (int u = 0; u < kGxServeUnroll; ++u) {
         const unsigned i = unsigned(u) * kGxServeThreads + threadIdx.x;
@@ -403,6 +430,7 @@ __global__ void __launch_bounds__(kGxThreads, 3) gx_place_kernel(gx_requester_t<
             const unsigned i = unsigned(k) * kGxThreads + tid;
             if (i < total) {
                 const unsigned b = s_bkt[i];
+                SCLX_GX_ASSERT(b < nb && i >= s_start[b] && i - s_start[b] < s_take[b]);
                 v[k]             = __ldcs(s_run[b] + (i - s_start[b]));
                 p[k]             = __ldcs(rq.pos + tbase + i);
             }
@@ -411,6 +439,7 @@ __global__ void __launch_bounds__(kGxThreads, 3) gx_place_kernel(gx_requester_t<
         for (int k = 0; k < kGxPerThread; ++k) {
             const unsigned i = unsigned(k) * kGxThreads + tid;
             if (i < total) {
+                SCLX_GX_ASSERT(p[k] < avail);
                 s_val[p[k]] = v[k];
                 if (total != avail) atomicOr(&s_written[p[k] >> 5], 1u << (p[k] & 31));
             }

@@ -251,6 +251,21 @@ def test_binned_gather_selfcheck_large(binaries, tmp_path, emulate, n, region_kb
     assert (int(bad), int(count)) == (0, n)
 
 
+@pytest.mark.parametrize("emulate", [None, 3])
+@pytest.mark.parametrize("case", ["gather_x_f32", "gather_x_f64", "gather_x_skew"])
+def test_binned_gather_with_bounds_checks_compiled_in(oracle, tmp_path, case, emulate):
+    """the gather cases against the driver built with -DSCLX_GX_CHECKS: every queue, response and
+    shared-memory index of the three kernels is checked on the device and a violation traps
+    (compute-sanitizer is not available on the pool)"""
+    checked = os.path.join(REPO, "drivers", "bin", "parity_driver_ours_checked")
+    if not os.path.exists(checked):
+        pytest.fail(f"{checked} is missing: run `python -c 'import __graft_entry__ as g; g.build()'`")
+    n, dtype, tol = CASES[case]
+    out = str(tmp_path / "checked.bin")
+    run_dump(checked, case, n, out, emulate)
+    compare(np.fromfile(out, dtype=dtype), oracle_expected(oracle, case, n), tol, f"{case} (checked build)")
+
+
 def run_example(name, emulate=None, timeout=900):
     exe = os.path.join(EXDIR, "ex_" + name)
     if not os.path.exists(exe):
